@@ -1,0 +1,120 @@
+/* libunast_spectral -- C ABI of the B200 (sm_100a) spectral signal path of Lucaskabela/UNAST.
+ *
+ * The reference has no FFI layer for this path: the boundary is two Python functions
+ * (src/utils.py:235 get_spectrograms, src/utils.py:281 spectrogram2wav), one script loop
+ * (src/gl_vocoder.py:10 vocode) and the .npy layout written at src/prepare_data.py:33-34.
+ * The entry points below are what a ctypes binding for those call sites needs; INTEGRATION.md
+ * shows the reference-side stub.  Every entry point cites the reference lines it replaces.
+ *
+ * Conventions
+ *   - all data pointers are DEVICE pointers owned by the caller (e.g. torch tensors' data_ptr());
+ *     `*_host` arguments are host arrays read before the call returns;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), allocates nothing,
+ *     and returns 0 on success or a negative UNAST_E_* code (message: unast_last_error());
+ *   - one context per (device, host thread); audio constants are those of
+ *     src/audio_parameters.py:1-20 (sr 22050, n_fft 2048, hop 275, win 1102, 80 mels,
+ *     preemphasis 0.97, ref_db 20, max_db 100) and are compiled in;
+ *   - there is no CPU fallback: without a CUDA device unast_create fails.
+ */
+#ifndef UNAST_SPECTRAL_H_
+#define UNAST_SPECTRAL_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UNAST_ABI_VERSION 1
+
+#define UNAST_OK 0
+#define UNAST_E_CUDA (-1)      /* a CUDA runtime call failed */
+#define UNAST_E_ARG (-2)       /* invalid argument */
+#define UNAST_E_WORKSPACE (-3) /* workspace too small */
+#define UNAST_E_DATA (-4)      /* data-dependent failure reported by a kernel (unast_check) */
+
+/* sample formats of `wave` (librosa.load gives float32; LJSpeech files are PCM16 = value / 32768) */
+#define UNAST_F32 0
+#define UNAST_I16 1
+
+/* arithmetic of the front-end FFT.  F64 mirrors numpy.fft (float64) as used by librosa.stft and is the
+ * mode that meets the 1e-4 parity gate on every bin; F32 is ~2x faster, max error ~2.5e-4 on bins that
+ * sit 90 dB below the frame peak ("precision"). */
+#define UNAST_PREC_F32 0
+#define UNAST_PREC_F64 1
+
+/* mel output layouts */
+#define UNAST_MEL_MAJOR_PER_UTT 0 /* utterance b: float[80][T_b] at 80*frame_off[b] == payload of the
+                                     fortran_order (T_b, 80) .pt.npy written at prepare_data.py:33 */
+#define UNAST_MEL_PADDED_BTM 1    /* float[B][T_max][80], rows t >= T_b untouched (caller zero-fills):
+                                     the batch tensor of preprocess.py:82-121 collate_fn_transformer */
+
+typedef struct unast_ctx unast_ctx;
+
+int unast_abi_version(void);
+const char* unast_last_error(void);
+
+/* Builds the constant tables (periodic Hann, twiddles, Slaney filterbank = librosa.filters.mel at
+ * utils.py:263, window-sum envelope) in float64 on the host and uploads them to `device`. */
+int unast_create(int device, unast_ctx** out);
+int unast_destroy(unast_ctx* ctx);
+int unast_num_sms(const unast_ctx* ctx);
+
+/* Blocks until `stream` is idle and returns UNAST_E_DATA if any kernel flagged a data error since the
+ * last check (utterance too short for reflect padding, empty signal after trimming). */
+int unast_check(unast_ctx* ctx, void* stream);
+
+/* The 80 x 1025 filterbank the context uses (row-major float32), for inspection / tests. */
+int unast_get_mel_basis(const unast_ctx* ctx, float* out_host);
+
+/* ---- forward path: utils.get_spectrograms (utils.py:235-278) -------------------------------- */
+
+/* librosa.effects.trim(y) of utils.py:248 / :304 / gl_vocoder.py:32 (top_db 60, frame 2048, hop 512).
+ * wave: B utterances back to back; wave_off[B+1] (device, int64) their first samples.
+ * bounds_out[B][2] (device, int32) receives start / end relative to each utterance.
+ * max_len = longest utterance in samples (host-known).  workspace >= unast_trim_workspace_bytes. */
+size_t unast_trim_workspace_bytes(int B, int max_len);
+int unast_trim_bounds(unast_ctx* ctx, const void* wave, int dtype, const int64_t* wave_off, int B, int max_len,
+                      int32_t* bounds_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* frame_off[B+1] (device, int32) = prefix sum of T_b = 1 + (end_b - start_b) / 275 (librosa.stft, center=True). */
+int unast_frame_offsets(unast_ctx* ctx, const int32_t* bounds, int B, int32_t* frame_off_out, void* stream);
+
+/* utils.py:251-276: pre-emphasis, STFT(2048/275/1102 Hann), |.|, mel projection, dB, normalisation.
+ * mag_out: float[sum T][1025] (utterance b's rows at frame_off[b]; == payload of the C-ordered
+ * (T_b, 1025) .mag.npy of prepare_data.py:34) or NULL to skip it (loader path).
+ * workspace >= unast_frontend_workspace_bytes(B). */
+size_t unast_frontend_workspace_bytes(int B);
+int unast_frontend(unast_ctx* ctx, const void* wave, int dtype, const int64_t* wave_off, const int32_t* bounds,
+                   const int32_t* frame_off, int B, int precision, float* mel_out, int mel_layout, int T_max,
+                   float* mag_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- inverse path: utils.spectrogram2wav (utils.py:281-306) / gl_vocoder.vocode (gl_vocoder.py:14-32) */
+
+/* mag_norm: float[sum T][1025] normalised magnitudes; frames_host[B] = T_b (host; every T_b >= 5).
+ * n_iter / momentum / angles0 select the variant:
+ *   utils.griffin_lim (utils.py:309-320): momentum = 0, angles0 = NULL (zero phase), n_iter = ap.n_iter
+ *   librosa.griffinlim (gl_vocoder.py:26): momentum = 0.99, n_iter = 32, angles0 = exp(2 pi i U)
+ * angles0: complex64[sum T][1025] (interleaved re,im; frame-major) or NULL.
+ * power = ap.power (1.2) de-normalises mag_norm as utils.py:289-298 does; power = 0 means mag_norm already is
+ * the linear target magnitude S (utils.griffin_lim / invert_spectrogram called directly).
+ * deemphasis != 0 applies lfilter([1],[1,-0.97]) in float64 (utils.py:301).
+ * wav_out: float[sum 275 (T_b - 1)], utterance b at wav_off = prefix sum.
+ * bounds_out (device int32 [B][2]) receives librosa.effects.trim bounds of each output (utils.py:304) or NULL. */
+size_t unast_griffinlim_workspace_bytes(const int32_t* frames_host, int B, float momentum);
+int unast_griffinlim(unast_ctx* ctx, const float* mag_norm, const int32_t* frames_host, int B, int n_iter,
+                     float momentum, const float* angles0, float power, int deemphasis, float* wav_out,
+                     int32_t* bounds_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- diagnostics (used by the test-suite to pin the FFT core on its own) --------------------- */
+
+/* frames: float[F][2048] whose samples [1102, 2048) are zero; out: complex64[F][1025] = rfft(frame). */
+int unast_debug_rfft(unast_ctx* ctx, const float* frames, int F, int precision, float* out, void* stream);
+/* spec: complex64[F][1025]; out: float[F][1102] = first 1102 samples of irfft(spec, 2048). */
+int unast_debug_irfft(unast_ctx* ctx, const float* spec, int F, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UNAST_SPECTRAL_H_ */

@@ -1,0 +1,97 @@
+// Shared constants and small device helpers for the UNAST spectral kernels (sm_100a).
+// Audio constants mirror reference src/audio_parameters.py:1-20.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <type_traits>
+#include <cfloat>
+#include <climits>
+
+namespace unast {
+
+constexpr int SR = 22050;
+constexpr int NFFT = 2048;
+constexpr int NBINS = 1025;
+constexpr int HOP = 275;
+constexpr int WIN = 1102;
+constexpr int NMELS = 80;
+constexpr int WIN_LPAD = (NFFT - WIN) / 2;      // 473: librosa pad_center(hann(1102), 2048)
+constexpr int HALF = NFFT / 2;                  // 1024: centre padding of stft/istft
+constexpr int NLIVE_C = WIN / 2;                // 551 packed complex inputs are non-zero
+constexpr int OVERLAP = WIN - HOP;              // 827 samples shared with following frames
+constexpr int TRIM_FRAME = 2048;
+constexpr int TRIM_HOP = 512;
+
+constexpr int S_STRIDE = 1032;                  // Griffin-Lim magnitude rows padded to a 32-byte multiple
+
+// ---- compile-time loop -------------------------------------------------------------------------
+template <int I, int N, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+    if constexpr (I < N) {
+        f(std::integral_constant<int, I>{});
+        static_for<I + 1, N>(f);
+    }
+}
+
+// ---- complex helpers (float2 / double2) --------------------------------------------------------
+template <class T> struct cplx;
+template <> struct cplx<float> { using type = float2; };
+template <> struct cplx<double> { using type = double2; };
+template <class T> using cplx_t = typename cplx<T>::type;
+
+__device__ __forceinline__ float2 mk(float x, float y) { return make_float2(x, y); }
+__device__ __forceinline__ double2 mk(double x, double y) { return make_double2(x, y); }
+
+#ifndef UNAST_PACKED_F32
+#define UNAST_PACKED_F32 0
+#endif
+
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) {
+#if UNAST_PACKED_F32
+    return __fadd2_rn(a, b);
+#else
+    return make_float2(a.x + b.x, a.y + b.y);
+#endif
+}
+__device__ __forceinline__ float2 csub(float2 a, float2 b) {
+#if UNAST_PACKED_F32
+    return __fadd2_rn(a, make_float2(-b.x, -b.y));
+#else
+    return make_float2(a.x - b.x, a.y - b.y);
+#endif
+}
+__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+
+// (a.x + i a.y) * (w.x + i w.y)
+__device__ __forceinline__ float2 cmul(float2 a, float2 w) {
+    return make_float2(fmaf(a.x, w.x, -(a.y * w.y)), fmaf(a.x, w.y, a.y * w.x));
+}
+__device__ __forceinline__ double2 cmul(double2 a, double2 w) {
+    return make_double2(fma(a.x, w.x, -(a.y * w.y)), fma(a.x, w.y, a.y * w.x));
+}
+
+__device__ __forceinline__ float fma_t(float a, float b, float c) { return fmaf(a, b, c); }
+__device__ __forceinline__ double fma_t(double a, double b, double c) { return fma(a, b, c); }
+
+// Window-sum-square envelope at padded position q of an utterance with T frames, accumulated exactly
+// like librosa.filters.window_sumsquare (float32 accumulator += float64 tap, ascending frame index).
+__device__ __forceinline__ float wss_at(int q, int T, const float* __restrict__ wss_per, const double* __restrict__ w2) {
+    const int c = q - WIN_LPAD;
+    if (c >= OVERLAP && c < HOP * T) return wss_per[c % HOP];
+    if (c < 0) return 0.0f;
+    int t_hi = min(T - 1, c / HOP);
+    int t_lo = c < WIN ? 0 : (c - WIN) / HOP + 1;
+    float acc = 0.0f;
+    for (int t = t_lo; t <= t_hi; ++t) acc = (float)((double)acc + w2[c - HOP * t]);
+    return acc;
+}
+
+// Error word layout shared by all kernels (unast_ctx::d_err): first non-zero code wins.
+enum DevErr : int {
+    ERR_NONE = 0,
+    ERR_TOO_SHORT = 1,     // an utterance is too short for reflect padding (librosa would raise too)
+    ERR_EMPTY = 2,         // trimmed signal is empty (reference: IndexError at utils.py:251)
+};
+
+}  // namespace unast

@@ -1,0 +1,180 @@
+// Warp-level 2048-point real FFT for sm_100a: one warp owns one frame.
+//
+// A real frame of 2048 samples (only the 1102 window taps are non-zero, circularly shifted so they
+// start at sample 0 -- a shift only multiplies bin k by a unit phase, which |X| ignores and the
+// Griffin-Lim forward/inverse pair cancels) is packed into 1024 complex points
+// z[n] = x[2n] + i x[2n+1] and transformed as 32 x 32:
+//   lane = n1, register = n2 (n = n1 + 32 n2)
+//   pass 1: 32-point FFT over the registers            (fft32, all in registers)
+//   twiddle W1024^(n1 k1) + transpose through shared memory (one exchange per FFT)
+//   pass 2: 32-point FFT over the registers            -> Z[k1 + 32 k2] in lane k1 / register k2
+//   real post-processing pairs bin k with 1024-k through a second shared-memory exchange.
+// The index algebra is validated on the CPU by tools/fft_model.py.
+//
+// Replaces numpy.fft.rfft / irfft as called by librosa.stft / istft on the reference path
+// (reference src/utils.py:254-257, :314, :328).
+#pragma once
+#include "common.cuh"
+
+namespace unast {
+
+// cos(2 pi j / 32), j = 0..8 (correctly rounded to double; float instantiations round once more).
+constexpr double kCos32[9] = {
+    1.0,
+    0.980785280403230449126182236134,
+    0.923879532511286756128183189397,
+    0.831469612302545237078788377618,
+    0.707106781186547524400844362105,
+    0.555570233019602224742830813949,
+    0.382683432365089771728459984030,
+    0.195090322016128267848284868477,
+    0.0};
+
+__host__ __device__ constexpr double cos32(int j) { return j <= 8 ? kCos32[j] : -kCos32[16 - j]; }   // j in 0..16
+__host__ __device__ constexpr double sin32(int j) { return j <= 8 ? kCos32[8 - j] : kCos32[j - 8]; }  // j in 0..16
+
+// a * exp(-2 pi i J / 32), J in 0..15 (forward DIF twiddles)
+template <int J, class C>
+__device__ __forceinline__ C mul_w32(C a) {
+    using T = decltype(a.x);
+    if constexpr (J == 0) {
+        return a;
+    } else if constexpr (J == 8) {
+        return mk(a.y, -a.x);
+    } else if constexpr (J == 4) {
+        constexpr T r = (T)kCos32[4];
+        return mk((a.x + a.y) * r, (a.y - a.x) * r);
+    } else if constexpr (J == 12) {
+        constexpr T r = (T)kCos32[4];
+        return mk((a.y - a.x) * r, -(a.x + a.y) * r);
+    } else {
+        constexpr T c = (T)cos32(J), s = (T)sin32(J);   // W = c - i s
+        return mk(fma_t(a.x, c, a.y * s), fma_t(a.y, c, -(a.x * s)));
+    }
+}
+
+__host__ __device__ constexpr int brev5(int i) {
+    return ((i & 1) << 4) | ((i & 2) << 2) | (i & 4) | ((i & 8) >> 2) | ((i & 16) >> 4);
+}
+
+template <int SPAN, class C>
+__device__ __forceinline__ void dif_stage(C (&v)[32]) {
+    static_for<0, 16>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        constexpr int base = (i / SPAN) * 2 * SPAN, j = i % SPAN;
+        C a = v[base + j], b = v[base + j + SPAN];
+        v[base + j] = cadd(a, b);
+        v[base + j + SPAN] = mul_w32<j*(16 / SPAN)>(csub(a, b));
+    });
+}
+
+// In-register 32-point forward FFT (radix-2 DIF, natural order in and out).
+// NZ: only v[0..NZ) are non-zero on entry (16 <= NZ <= 32) -- prunes the first stage.
+template <int NZ, class C>
+__device__ __forceinline__ void fft32(C (&v)[32]) {
+    static_assert(NZ >= 16 && NZ <= 32, "pruning supports 16..32 live inputs");
+    static_for<0, 16>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        if constexpr (j + 16 < NZ) {
+            C a = v[j], b = v[j + 16];
+            v[j] = cadd(a, b);
+            v[j + 16] = mul_w32<j>(csub(a, b));
+        } else {
+            v[j + 16] = mul_w32<j>(v[j]);
+        }
+    });
+    dif_stage<8>(v);
+    dif_stage<4>(v);
+    dif_stage<2>(v);
+    dif_stage<1>(v);
+    C t[32];
+    static_for<0, 32>([&](auto kk) { constexpr int k = decltype(kk)::value; t[k] = v[brev5(k)]; });
+    static_for<0, 32>([&](auto kk) { constexpr int k = decltype(kk)::value; v[k] = t[k]; });
+}
+
+// Row stride (in complex elements) of a warp's exchange buffer: 128-bit reads of a lane's own row are
+// bank-conflict-free for float2 with stride 34 (272 B) and for double2 with stride 33 (528 B).
+template <class T> struct XchStride;
+template <> struct XchStride<float> { static constexpr int value = 34; };
+template <> struct XchStride<double> { static constexpr int value = 33; };
+template <class T> __host__ __device__ constexpr int xch_elems() { return 32 * XchStride<T>::value; }   // >= 1025
+
+// 1024-point complex forward FFT across one warp.
+// in : v[n2] = z[lane + 32 n2]      (only the first NZ registers non-zero)
+// out: v[k2] = Z[lane + 32 k2]
+// tw : [k1][n1] table of W1024^(n1 k1) (shared or global memory)
+template <class T, int NZ>
+__device__ __forceinline__ void warp_fft1024(cplx_t<T> (&v)[32], cplx_t<T>* xch, const cplx_t<T>* __restrict__ tw,
+                                             int lane) {
+    using C = cplx_t<T>;
+    constexpr int XS = XchStride<T>::value;
+    fft32<NZ>(v);
+    static_for<0, 32>([&](auto kk) {
+        constexpr int k1 = decltype(kk)::value;
+        C a = v[k1];
+        if constexpr (k1 > 0) a = cmul(a, tw[k1 * 32 + lane]);
+        xch[k1 * XS + lane] = a;
+    });
+    __syncwarp();
+    if constexpr (sizeof(T) == 4) {
+        const float4* row = reinterpret_cast<const float4*>(xch + lane * XS);
+        static_for<0, 16>([&](auto ii) {
+            constexpr int i = decltype(ii)::value;
+            float4 q = row[i];
+            v[2 * i] = mk((T)q.x, (T)q.y);
+            v[2 * i + 1] = mk((T)q.z, (T)q.w);
+        });
+    } else {
+        const C* row = xch + lane * XS;
+        static_for<0, 32>([&](auto ii) { constexpr int i = decltype(ii)::value; v[i] = row[i]; });
+    }
+    __syncwarp();
+    fft32<32>(v);
+}
+
+// Real-FFT post-processing.  in: v[j] = Z[lane + 32 j]; out: v[j] = X[lane + 32 j], nyq = X[1024] (all lanes).
+// wp[k] = (-sin(th)/2, -cos(th)/2), th = 2 pi k / 2048, k = 0..1023.
+template <class T>
+__device__ __forceinline__ void rfft_post(cplx_t<T> (&v)[32], T& nyq, cplx_t<T>* xch, const cplx_t<T>* __restrict__ wp,
+                                          int lane) {
+    using C = cplx_t<T>;
+    static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; xch[lane + 32 * j] = v[j]; });
+    if (lane == 0) xch[1024] = v[0];
+    __syncwarp();
+    C z0 = xch[0];
+    nyq = z0.x - z0.y;
+    static_for<0, 32>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        const int k = lane + 32 * j;
+        C z = v[j], p = xch[1024 - k], w = wp[k];
+        T er = (T)0.5 * (z.x + p.x), ei = (T)0.5 * (z.y - p.y);
+        T orr = z.x - p.x, oi = z.y + p.y;
+        v[j] = mk(fma_t(w.x, orr, fma_t(-w.y, oi, er)), fma_t(w.x, oi, fma_t(w.y, orr, ei)));
+    });
+    __syncwarp();
+}
+
+// Inverse of rfft_post followed by conjugation, i.e. the input of the forward machinery that yields
+// conj(irfft) * 1024.  in: v[j] = X[lane + 32 j], nyq = X[1024]; out: v[j] = conj(Z'[lane + 32 j]).
+template <class T>
+__device__ __forceinline__ void irfft_pre(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* xch, const cplx_t<T>* __restrict__ wp,
+                                          int lane) {
+    using C = cplx_t<T>;
+    static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; xch[lane + 32 * j] = v[j]; });
+    if (lane == 0) xch[1024] = mk(nyq, (T)0);
+    __syncwarp();
+    static_for<0, 32>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        const int k = lane + 32 * j;
+        C x = v[j], p = xch[1024 - k], w = wp[k];
+        T er = (T)0.5 * (x.x + p.x), ei = (T)0.5 * (x.y - p.y);
+        T dr = x.x - p.x, di = x.y + p.y;
+        // Z' = (er, ei) + conj(w) * (dr, di);   conj(w) = (w.x, -w.y)
+        T zr = fma_t(w.x, dr, fma_t(w.y, di, er));
+        T zi = fma_t(w.x, di, fma_t(-w.y, dr, ei));
+        v[j] = mk(zr, -zi);
+    });
+    __syncwarp();
+}
+
+}  // namespace unast

@@ -1,0 +1,251 @@
+// K0 / K2 / K4: silence trimming (librosa.effects.trim, reference src/utils.py:248,304 and
+// src/gl_vocoder.py:32), magnitude de-normalisation (utils.py:289-298) and de-emphasis
+// (scipy.signal.lfilter([1],[1,-0.97]), utils.py:301).
+#pragma once
+#include <cfloat>
+#include "common.cuh"
+
+namespace unast {
+
+__device__ __forceinline__ float ld_sample(const void* wave, int is_i16, long long idx) {
+    if (is_i16) return (float)reinterpret_cast<const short*>(wave)[idx] * (1.0f / 32768.0f);
+    return reinterpret_cast<const float*>(wave)[idx];
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// energy of every 512-sample block of every utterance: be[b * nblk_max + j] = sum y^2 over block j
+__global__ void block_energy_kernel(const void* wave, int is_i16, const long long* __restrict__ off, int B,
+                                    int nblk_max, double* __restrict__ be) {
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const long long base = off[b];
+    const int N = (int)(off[b + 1] - base);
+    if (j >= nblk_max || j * TRIM_HOP >= N) return;
+    const int lo = j * TRIM_HOP, hi = min(N, lo + TRIM_HOP);
+    double e = 0.0;
+    for (int n = lo + lane; n < hi; n += 32) { double y = ld_sample(wave, is_i16, base + n); e += y * y; }
+    e = warp_sum(e);
+    if (lane == 0) be[(size_t)b * nblk_max + j] = e;
+}
+
+// One CTA per utterance: frame mean-square over reflect-padded 2048-sample frames (hop 512), threshold
+// at -60 dB below the loudest frame, first / last non-silent frame -> [start, end).
+__global__ void __launch_bounds__(128) trim_decide_kernel(const void* wave, int is_i16, const long long* __restrict__ off,
+                                                          int nblk_max, const double* __restrict__ be,
+                                                          int* __restrict__ bounds, int* err) {
+    __shared__ double s_red[4];
+    __shared__ double s_edge[8];
+    __shared__ int s_first[4], s_last[4];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long base = off[b];
+    const int N = (int)(off[b + 1] - base);
+    if (N <= TRIM_FRAME / 2) {                       // np.pad(..., 'reflect') needs N > 1024
+        if (tid == 0) { bounds[2 * b] = 0; bounds[2 * b + 1] = 0; atomicCAS(err, ERR_NONE, ERR_TOO_SHORT); }
+        return;
+    }
+    const int nfr = 1 + N / TRIM_HOP;
+    const double* beb = be + (size_t)b * nblk_max;
+
+    // reflected contributions exist only for frames 0, 1 (left) and the last <= 3 frames (right):
+    // slots 0,1 = left part of frames 0,1; slots 2..4 = right part of frames nfr-3 .. nfr-1
+    for (int e = 0; e < 5; ++e) {
+        int i, lo, hi;                               // reflected source range [lo, hi] (inclusive) of frame i
+        if (e < 2) { i = e; lo = 1; hi = TRIM_FRAME / 2 - TRIM_HOP * i; }
+        else {
+            i = nfr - 5 + e;
+            const int last = TRIM_HOP * i + TRIM_FRAME / 2 - 1;      // last signal index the frame touches
+            lo = 2 * (N - 1) - last; hi = N - 2;
+        }
+        double part = 0.0;
+        if (i >= 0 && i < nfr && hi >= lo) {
+            for (int n = lo + tid; n <= hi; n += 128) { double y = ld_sample(wave, is_i16, base + n); part += y * y; }
+        }
+        part = warp_sum(part);
+        if (lane == 0) s_red[warp] = part;
+        __syncthreads();
+        if (tid == 0) s_edge[e] = s_red[0] + s_red[1] + s_red[2] + s_red[3];
+        __syncthreads();
+    }
+
+    auto frame_energy = [&](int i) -> double {
+        const int lo = max(0, TRIM_HOP * i - TRIM_FRAME / 2), hi = min(N, TRIM_HOP * i + TRIM_FRAME / 2);
+        double e = 0.0;
+        for (int j = lo / TRIM_HOP; j * TRIM_HOP < hi; ++j) e += beb[j];
+        if (i < 2) e += s_edge[i];
+        if (i >= nfr - 3 && TRIM_HOP * i + TRIM_FRAME / 2 > N) e += s_edge[2 + (i - (nfr - 3))];
+        return e;
+    };
+
+    double emax = 0.0;
+    for (int i = tid; i < nfr; i += 128) emax = fmax(emax, frame_energy(i));
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) emax = fmax(emax, __shfl_xor_sync(0xffffffffu, emax, d));
+    if (lane == 0) s_red[warp] = emax;
+    __syncthreads();
+    emax = fmax(fmax(s_red[0], s_red[1]), fmax(s_red[2], s_red[3]));
+    const double ref_db = 10.0 * log10(fmax(1e-10, emax / TRIM_FRAME));
+    int first = INT_MAX, last = -1;
+    for (int i = tid; i < nfr; i += 128) {
+        const double db = 10.0 * log10(fmax(1e-10, frame_energy(i) / TRIM_FRAME)) - ref_db;
+        if (db > -60.0) { first = min(first, i); last = max(last, i); }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        first = min(first, __shfl_xor_sync(0xffffffffu, first, d));
+        last = max(last, __shfl_xor_sync(0xffffffffu, last, d));
+    }
+    if (lane == 0) { s_first[warp] = first; s_last[warp] = last; }
+    __syncthreads();
+    if (tid == 0) {
+        first = min(min(s_first[0], s_first[1]), min(s_first[2], s_first[3]));
+        last = max(max(s_last[0], s_last[1]), max(s_last[2], s_last[3]));
+        if (last < 0) { bounds[2 * b] = 0; bounds[2 * b + 1] = 0; }
+        else { bounds[2 * b] = first * TRIM_HOP; bounds[2 * b + 1] = min(N, (last + 1) * TRIM_HOP); }
+    }
+}
+
+// frame_off[b] = prefix sum of T_b = 1 + (end - start) / 275 (librosa.stft, center=True); single CTA.
+__global__ void __launch_bounds__(1024) frame_offsets_kernel(const int* __restrict__ bounds, int B, int* __restrict__ frame_off,
+                                                             int* err) {
+    __shared__ int s_warp[32];
+    __shared__ int s_total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { s_total = 0; frame_off[0] = 0; }
+    __syncthreads();
+    for (int base = 0; base < B; base += 1024) {
+        const int b = base + tid;
+        int T = 0;
+        if (b < B) {
+            const int N = bounds[2 * b + 1] - bounds[2 * b];
+            if (N <= 0) atomicCAS(err, ERR_NONE, ERR_EMPTY);
+            else if (N <= HALF) atomicCAS(err, ERR_NONE, ERR_TOO_SHORT);
+            else T = 1 + N / HOP;
+        }
+        int x = T;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+        if (lane == 31) s_warp[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { int y = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += y; }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const int incl = x + (warp ? s_warp[warp - 1] : 0) + s_total;
+        if (b < B) frame_off[b + 1] = incl;
+        __syncthreads();
+        if (tid == 1023) s_total = incl;
+        __syncthreads();
+    }
+}
+
+// step_off[b] = prefix sum of ceil(T_b / fps); single CTA (same scan, different summand).
+__global__ void __launch_bounds__(1024) step_offsets_kernel(const int* __restrict__ frame_off, int B, int fps,
+                                                            int* __restrict__ step_off) {
+    __shared__ int s_warp[32];
+    __shared__ int s_total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { s_total = 0; step_off[0] = 0; }
+    __syncthreads();
+    for (int base = 0; base < B; base += 1024) {
+        const int b = base + tid;
+        int x = b < B ? (frame_off[b + 1] - frame_off[b] + fps - 1) / fps : 0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+        if (lane == 31) s_warp[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { int y = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += y; }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const int incl = x + (warp ? s_warp[warp - 1] : 0) + s_total;
+        if (b < B) step_off[b + 1] = incl;
+        __syncthreads();
+        if (tid == 1023) s_total = incl;
+        __syncthreads();
+    }
+}
+
+// K2: S = (10^((clip(m,0,1)*max_db - max_db + ref_db) * 0.05))^power, float32 (utils.py:289-298).
+// power == 0 passes `mag` through unchanged (griffin_lim / invert_spectrogram called on a linear spectrogram).
+__global__ void gl_prepare_kernel(const float* __restrict__ mag, long long total_frames, float power, float* __restrict__ S) {
+    const long long n = total_frames * NBINS;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / NBINS;
+        const int k = (int)(i - r * NBINS);
+        if (power == 0.0f) { S[r * S_STRIDE + k] = mag[i]; continue; }   // input already is the linear target magnitude
+        float m = fminf(fmaxf(mag[i], 0.0f), 1.0f);
+        m = m * 100.0f - 100.0f + 20.0f;
+        const float a = powf(10.0f, m * 0.05f);
+        S[r * S_STRIDE + k] = powf(a, power);
+    }
+}
+
+// K4: y[n] = x[n] + 0.97 y[n-1] in float64 (scipy.signal.lfilter), x = ola / wss on the fly, float32 out.
+// A warp owns a chunk; the recurrence is restarted `WARM` samples early (0.97^2048 ~ 1e-27, far below
+// float64 resolution), so chunks are independent.  Within the chunk: 32-sample inclusive scans with carry.
+struct DeemphParams {
+    const float* ola;            // padded OLA sums, or nullptr when `x` is given
+    const float* x;              // plain input signal (already normalised), or nullptr
+    const int* frame_off;
+    const long long* pad_off;
+    const long long* wav_off;    // [B+1]
+    float* out;
+    const float* wss_per;
+    const double* w2;
+    double coef;                 // 0.97, or 0 to skip de-emphasis (copy / normalise only)
+};
+
+constexpr int DE_CHUNK = 4096;
+constexpr int DE_WARM = 2048;
+
+__global__ void deemph_kernel(const DeemphParams P) {
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int chunk = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int L = (int)(P.wav_off[b + 1] - P.wav_off[b]);
+    const int c0 = chunk * DE_CHUNK;
+    if (c0 >= L) return;
+    const int c1 = min(L, c0 + DE_CHUNK);
+    const int Tb = P.frame_off ? P.frame_off[b + 1] - P.frame_off[b] : 0;
+    const float* src = P.ola ? P.ola + P.pad_off[b] + HALF : P.x + P.wav_off[b];
+    float* dst = P.out + P.wav_off[b];
+    const double a = P.coef;
+    double apow[5];
+    apow[0] = a;
+#pragma unroll
+    for (int i = 1; i < 5; ++i) apow[i] = apow[i - 1] * apow[i - 1];
+    double alane = a;                                   // a^(lane+1)
+    for (int i = 0; i < lane; ++i) alane *= a;
+    double carry = 0.0;
+    for (int n0 = max(0, c0 - DE_WARM) & ~31; n0 < c1; n0 += 32) {
+        const int n = n0 + lane;
+        double v = 0.0;
+        if (n < c1) {
+            float y = src[n];
+            if (P.ola) { const float w = wss_at(n + HALF, Tb, P.wss_per, P.w2); if (w > FLT_MIN) y = y / w; }
+            v = (double)y;
+        }
+#pragma unroll
+        for (int s = 0; s < 5; ++s) {
+            const double t = __shfl_up_sync(0xffffffffu, v, 1 << s);
+            if (lane >= (1 << s)) v = fma(apow[s], t, v);
+        }
+        v = fma(alane, carry, v);
+        carry = __shfl_sync(0xffffffffu, v, 31);
+        if (n >= c0 && n < c1) dst[n] = (float)v;
+    }
+}
+
+}  // namespace unast

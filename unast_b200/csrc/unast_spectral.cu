@@ -1,0 +1,454 @@
+// libunast_spectral.so -- host side of the C ABI declared in include/unast_spectral.h:
+// constant tables (built in float64 on the host), launch logic, diagnostics.  No torch types here.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/unast_spectral.h"
+#include "frontend.cuh"
+#include "griffinlim.cuh"
+#include "trim.cuh"
+
+using namespace unast;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+
+#define CU(expr)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (expr);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(UNAST_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));         \
+    } while (0)
+
+constexpr double kPi = 3.14159265358979323846264338327950288;
+
+size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+float tf32_rna(float x) {
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    u += 0x1000u;
+    u &= 0xffffe000u;
+    memcpy(&x, &u, 4);
+    return x;
+}
+
+// ---- librosa.filters.mel(22050, 2048, 80): Slaney scale, area-normalised, float32 ----
+double hz_to_mel(double f) {
+    const double f_sp = 200.0 / 3, min_log_hz = 1000.0, min_log_mel = min_log_hz / f_sp, logstep = std::log(6.4) / 27.0;
+    return f >= min_log_hz ? min_log_mel + std::log(f / min_log_hz) / logstep : f / f_sp;
+}
+double mel_to_hz(double m) {
+    const double f_sp = 200.0 / 3, min_log_hz = 1000.0, min_log_mel = min_log_hz / f_sp, logstep = std::log(6.4) / 27.0;
+    return m >= min_log_mel ? min_log_hz * std::exp(logstep * (m - min_log_mel)) : f_sp * m;
+}
+std::vector<float> build_mel_basis() {
+    const double fmax = SR / 2.0;
+    std::vector<double> fftfreqs(NBINS), mel_f(NMELS + 2);
+    for (int i = 0; i < NBINS; ++i) fftfreqs[i] = i * (fmax / (NBINS - 1));
+    fftfreqs[NBINS - 1] = fmax;
+    const double m0 = hz_to_mel(0.0), m1 = hz_to_mel(fmax), step = (m1 - m0) / (NMELS + 1);
+    for (int i = 0; i < NMELS + 2; ++i) mel_f[i] = mel_to_hz(i == NMELS + 1 ? m1 : m0 + step * i);
+    std::vector<float> w((size_t)NMELS * NBINS);
+    for (int i = 0; i < NMELS; ++i) {
+        const double fd0 = mel_f[i + 1] - mel_f[i], fd1 = mel_f[i + 2] - mel_f[i + 1];
+        const double enorm = 2.0 / (mel_f[i + 2] - mel_f[i]);
+        for (int k = 0; k < NBINS; ++k) {
+            const double lower = -(mel_f[i] - fftfreqs[k]) / fd0, upper = (mel_f[i + 2] - fftfreqs[k]) / fd1;
+            const float tri = (float)std::fmax(0.0, std::fmin(lower, upper));
+            w[(size_t)i * NBINS + k] = (float)((double)tri * enorm);
+        }
+    }
+    return w;
+}
+
+template <class T>
+cudaError_t upload(T** dptr, const std::vector<T>& h) {
+    cudaError_t e = cudaMalloc((void**)dptr, h.size() * sizeof(T));
+    if (e != cudaSuccess) return e;
+    return cudaMemcpy(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+}  // namespace
+
+struct unast_ctx {
+    int device = 0;
+    int num_sms = 0;
+    float2 *win2_f = nullptr, *wini2_f = nullptr, *tw_f = nullptr, *wp_f = nullptr, *phi_f = nullptr;
+    double2 *win2_d = nullptr, *tw_d = nullptr, *wp_d = nullptr;
+    float* wss_per = nullptr;
+    double* w2 = nullptr;
+    float4* bfrag = nullptr;
+    int* pair_kb = nullptr;
+    int pair_begin[11] = {0};
+    int* d_err = nullptr;
+    std::vector<float> mel_basis;
+};
+
+// ---- diagnostics kernels ----------------------------------------------------------------------
+namespace unast {
+
+template <class T>
+__global__ void __launch_bounds__(128) debug_rfft_kernel(const float* __restrict__ frames, int F, const cplx_t<T>* tw,
+                                                         const cplx_t<T>* wp, float2* __restrict__ out) {
+    using C = cplx_t<T>;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    C* xch = reinterpret_cast<C*>(smem) + warp * xch_elems<T>();
+    const int f = blockIdx.x * 4 + warp;
+    if (f >= F) return;
+    const float2* src = reinterpret_cast<const float2*>(frames + (size_t)f * NFFT);
+    C v[32];
+    static_for<0, 18>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        const int n = lane + 32 * j;
+        if (j < 17 || n < NLIVE_C) { float2 s = src[n]; v[j] = mk((T)s.x, (T)s.y); } else v[j] = mk((T)0, (T)0);
+    });
+    warp_fft1024<T, 18>(v, xch, tw, lane);
+    T nyq;
+    rfft_post<T>(v, nyq, xch, wp, lane);
+    float2* dst = out + (size_t)f * NBINS;
+    static_for<0, 32>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        dst[lane + 32 * j] = make_float2((float)v[j].x, (float)v[j].y);
+    });
+    if (lane == 0) dst[1024] = make_float2((float)nyq, 0.f);
+}
+
+__global__ void __launch_bounds__(128) debug_irfft_kernel(const float2* __restrict__ spec, int F, const float2* tw,
+                                                          const float2* wp, float* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xch = reinterpret_cast<float2*>(smem) + warp * xch_elems<float>();
+    const int f = blockIdx.x * 4 + warp;
+    if (f >= F) return;
+    const float2* src = spec + (size_t)f * NBINS;
+    float2 v[32];
+    static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = src[lane + 32 * j]; });
+    if (lane == 0) v[0].y = 0.f;
+    float nyq = src[1024].x;
+    irfft_pre<float>(v, nyq, xch, wp, lane);
+    warp_fft1024<float, 32>(v, xch, tw, lane);
+    float2* dst = reinterpret_cast<float2*>(out + (size_t)f * WIN);
+    static_for<0, 18>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        const int n = lane + 32 * j;
+        if (j < 17 || n < NLIVE_C) dst[n] = make_float2(v[j].x * (1.0f / 1024.0f), -v[j].y * (1.0f / 1024.0f));
+    });
+}
+
+}  // namespace unast
+
+// ---- C ABI -------------------------------------------------------------------------------------
+extern "C" {
+
+int unast_abi_version(void) { return UNAST_ABI_VERSION; }
+const char* unast_last_error(void) { return g_err.c_str(); }
+
+int unast_create(int device, unast_ctx** out) {
+    if (!out) return fail(UNAST_E_ARG, "unast_create: out is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(UNAST_E_ARG, "unast_create: no such CUDA device (there is no CPU fallback)");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(UNAST_E_ARG, "unast_create: built for sm_100a (Blackwell B200) only");
+    unast_ctx* c = new unast_ctx();
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+
+    std::vector<double> hann(WIN);
+    for (int k = 0; k < WIN; ++k) hann[k] = 0.5 - 0.5 * std::cos(2.0 * kPi * k / WIN);
+    std::vector<float2> win2_f(NLIVE_C), wini2_f(NLIVE_C);
+    std::vector<double2> win2_d(NLIVE_C);
+    for (int n = 0; n < NLIVE_C; ++n) {
+        win2_d[n] = make_double2(hann[2 * n], hann[2 * n + 1]);
+        win2_f[n] = make_float2((float)hann[2 * n], (float)hann[2 * n + 1]);
+        wini2_f[n] = make_float2((float)(hann[2 * n] / 1024.0), (float)(hann[2 * n + 1] / 1024.0));
+    }
+    std::vector<float2> tw_f(1024), wp_f(1024), phi_f(NBINS);
+    std::vector<double2> tw_d(1024), wp_d(1024);
+    for (int k1 = 0; k1 < 32; ++k1)
+        for (int n1 = 0; n1 < 32; ++n1) {
+            const double th = 2.0 * kPi * ((k1 * n1) % 1024) / 1024.0;
+            tw_d[k1 * 32 + n1] = make_double2(std::cos(th), -std::sin(th));
+            tw_f[k1 * 32 + n1] = make_float2((float)std::cos(th), (float)-std::sin(th));
+        }
+    for (int k = 0; k < 1024; ++k) {
+        const double th = 2.0 * kPi * k / 2048.0;
+        wp_d[k] = make_double2(-0.5 * std::sin(th), -0.5 * std::cos(th));
+        wp_f[k] = make_float2((float)(-0.5 * std::sin(th)), (float)(-0.5 * std::cos(th)));
+    }
+    for (int k = 0; k < NBINS; ++k) {
+        const double th = 2.0 * kPi * ((WIN_LPAD * k) % NFFT) / NFFT;
+        phi_f[k] = make_float2((float)std::cos(th), (float)std::sin(th));
+    }
+    std::vector<double> w2(WIN);
+    for (int k = 0; k < WIN; ++k) w2[k] = hann[k] * hann[k];
+    std::vector<float> wss_per(HOP);
+    for (int r = 0; r < HOP; ++r) {
+        float acc = 0.f;
+        int mmax = (WIN - 1 - r) / HOP;
+        for (int m = mmax; m >= 0; --m) acc = (float)((double)acc + w2[r + HOP * m]);   // ascending frame index
+        wss_per[r] = acc;
+    }
+
+    c->mel_basis = build_mel_basis();
+    for (int m = 0; m < NMELS; ++m)
+        if (c->mel_basis[(size_t)m * NBINS + 1024] != 0.f) { delete c; return fail(UNAST_E_ARG, "filterbank has weight on the Nyquist bin"); }
+    std::vector<float4> bfrag;
+    std::vector<int> pair_kb;
+    for (int nt = 0; nt < NMELS / 8; ++nt) {
+        c->pair_begin[nt] = (int)pair_kb.size();
+        for (int kb = 0; kb < 128; ++kb) {
+            bool any = false;
+            for (int g = 0; g < 8 && !any; ++g)
+                for (int t = 0; t < 8; ++t)
+                    if (c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t] != 0.f) { any = true; break; }
+            if (!any) continue;
+            pair_kb.push_back(kb);
+            for (int lane = 0; lane < 32; ++lane) {
+                const int g = lane >> 2, t = lane & 3;
+                const float b0 = c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t];
+                const float b1 = c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t + 4];
+                const float b0h = tf32_rna(b0), b1h = tf32_rna(b1);
+                bfrag.push_back(make_float4(b0h, b1h, tf32_rna(b0 - b0h), tf32_rna(b1 - b1h)));
+            }
+        }
+    }
+    c->pair_begin[NMELS / 8] = (int)pair_kb.size();
+
+    cudaError_t e = cudaSuccess;
+    auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
+    up(&c->win2_f, win2_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
+    up(&c->win2_d, win2_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
+    up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<float, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeLayout<float, 16>::bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<double, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeLayout<double, 8>::bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
+    if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
+    *out = c;
+    return UNAST_OK;
+}
+
+int unast_destroy(unast_ctx* c) {
+    if (!c) return UNAST_OK;
+    cudaFree(c->win2_f); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
+    cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
+    cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
+    delete c;
+    return UNAST_OK;
+}
+
+int unast_num_sms(const unast_ctx* c) { return c ? c->num_sms : 0; }
+
+int unast_check(unast_ctx* c, void* stream) {
+    if (!c) return fail(UNAST_E_ARG, "unast_check: ctx is NULL");
+    int h = 0;
+    CU(cudaMemcpyAsync(&h, c->d_err, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CU(cudaStreamSynchronize((cudaStream_t)stream));
+    if (h != ERR_NONE) {
+        CU(cudaMemsetAsync(c->d_err, 0, sizeof(int), (cudaStream_t)stream));
+        if (h == ERR_TOO_SHORT) return fail(UNAST_E_DATA, "an utterance is too short for reflect padding (needs > 1024 samples / >= 5 frames)");
+        if (h == ERR_EMPTY) return fail(UNAST_E_DATA, "an utterance is empty after trimming");
+        return fail(UNAST_E_DATA, "kernel reported data error " + std::to_string(h));
+    }
+    return UNAST_OK;
+}
+
+int unast_get_mel_basis(const unast_ctx* c, float* out_host) {
+    if (!c || !out_host) return fail(UNAST_E_ARG, "unast_get_mel_basis: NULL argument");
+    memcpy(out_host, c->mel_basis.data(), c->mel_basis.size() * sizeof(float));
+    return UNAST_OK;
+}
+
+// ---- trim ----
+static int nblk_of(int max_len) { return (max_len + TRIM_HOP - 1) / TRIM_HOP; }
+
+size_t unast_trim_workspace_bytes(int B, int max_len) { return align256((size_t)B * nblk_of(max_len) * sizeof(double)); }
+
+int unast_trim_bounds(unast_ctx* c, const void* wave, int dtype, const int64_t* wave_off, int B, int max_len,
+                      int32_t* bounds_out, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!c || !wave || !wave_off || !bounds_out || B <= 0 || max_len <= 0) return fail(UNAST_E_ARG, "unast_trim_bounds: bad argument");
+    if (dtype != UNAST_F32 && dtype != UNAST_I16) return fail(UNAST_E_ARG, "unast_trim_bounds: dtype must be UNAST_F32 or UNAST_I16");
+    if (workspace_bytes < unast_trim_workspace_bytes(B, max_len) || !workspace) return fail(UNAST_E_WORKSPACE, "unast_trim_bounds: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nblk = nblk_of(max_len);
+    dim3 grid((nblk + 7) / 8, B);
+    block_energy_kernel<<<grid, 256, 0, st>>>(wave, dtype == UNAST_I16, (const long long*)wave_off, B, nblk, (double*)workspace);
+    trim_decide_kernel<<<B, 128, 0, st>>>(wave, dtype == UNAST_I16, (const long long*)wave_off, nblk, (const double*)workspace, bounds_out, c->d_err);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+int unast_frame_offsets(unast_ctx* c, const int32_t* bounds, int B, int32_t* frame_off_out, void* stream) {
+    if (!c || !bounds || !frame_off_out || B <= 0) return fail(UNAST_E_ARG, "unast_frame_offsets: bad argument");
+    frame_offsets_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(bounds, B, frame_off_out, c->d_err);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+// ---- front end ----
+size_t unast_frontend_workspace_bytes(int B) { return align256((size_t)(B + 1) * sizeof(int)); }
+
+int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wave_off, const int32_t* bounds,
+                   const int32_t* frame_off, int B, int precision, float* mel_out, int mel_layout, int T_max,
+                   float* mag_out, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!c || !wave || !wave_off || !bounds || !frame_off || !mel_out || B <= 0) return fail(UNAST_E_ARG, "unast_frontend: bad argument");
+    if (dtype != UNAST_F32 && dtype != UNAST_I16) return fail(UNAST_E_ARG, "unast_frontend: dtype must be UNAST_F32 or UNAST_I16");
+    if (precision != UNAST_PREC_F32 && precision != UNAST_PREC_F64) return fail(UNAST_E_ARG, "unast_frontend: bad precision");
+    if (mel_layout != UNAST_MEL_MAJOR_PER_UTT && mel_layout != UNAST_MEL_PADDED_BTM) return fail(UNAST_E_ARG, "unast_frontend: bad mel_layout");
+    if (mel_layout == UNAST_MEL_PADDED_BTM && T_max <= 0) return fail(UNAST_E_ARG, "unast_frontend: T_max required for the padded layout");
+    if (!workspace || workspace_bytes < unast_frontend_workspace_bytes(B)) return fail(UNAST_E_WORKSPACE, "unast_frontend: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    int* step_off = (int*)workspace;
+    FrontendParams P;
+    P.wave = wave; P.wave_is_i16 = dtype == UNAST_I16; P.wave_off = (const long long*)wave_off; P.bounds = bounds;
+    P.frame_off = frame_off; P.step_off = step_off; P.B = B; P.mag_out = mag_out; P.mel_out = mel_out;
+    P.mel_layout = mel_layout; P.T_max = T_max;
+    P.mel.bfrag = c->bfrag; P.mel.pair_kb = c->pair_kb;
+    memcpy(P.mel.pair_begin, c->pair_begin, sizeof(P.mel.pair_begin));
+    P.err = c->d_err;
+    if (precision == UNAST_PREC_F32) {
+        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, 16, step_off);
+        P.win2 = c->win2_f; P.tw1024 = c->tw_f; P.wp = c->wp_f;
+        frontend_kernel<float, 16><<<c->num_sms, 16 * 32, FeLayout<float, 16>::bytes, st>>>(P);
+    } else {
+        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, 8, step_off);
+        P.win2 = c->win2_d; P.tw1024 = c->tw_d; P.wp = c->wp_d;
+        frontend_kernel<double, 8><<<c->num_sms, 8 * 32, FeLayout<double, 8>::bytes, st>>>(P);
+    }
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+// ---- Griffin-Lim ----
+namespace {
+struct GlPlan {
+    std::vector<int> frame_off, step_off;
+    std::vector<long long> pad_off, wav_off;
+    long long total_frames = 0, total_pad = 0, total_wav = 0;
+    int max_wav = 0;
+    size_t o_meta_i = 0, o_meta_l = 0, o_S = 0, o_ola = 0, o_tprev = 0, o_be = 0, bytes = 0;
+};
+bool gl_plan(const int32_t* frames, int B, float momentum, GlPlan& p) {
+    p.frame_off.assign(B + 1, 0); p.step_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.wav_off.assign(B + 1, 0);
+    for (int b = 0; b < B; ++b) {
+        const int T = frames[b];
+        if (T < 5) return false;                                    // reflect padding of the in-loop stft needs 275 (T-1) > 1024
+        p.frame_off[b + 1] = p.frame_off[b] + T;
+        p.step_off[b + 1] = p.step_off[b] + (T + GL_FPS - 1) / GL_FPS;
+        p.pad_off[b + 1] = p.pad_off[b] + NFFT + (long long)HOP * (T - 1);
+        p.wav_off[b + 1] = p.wav_off[b] + (long long)HOP * (T - 1);
+        p.max_wav = std::max(p.max_wav, HOP * (T - 1));
+    }
+    p.total_frames = p.frame_off[B]; p.total_pad = p.pad_off[B]; p.total_wav = p.wav_off[B];
+    size_t o = 0;
+    p.o_meta_i = o; o += align256(2 * (size_t)(B + 1) * sizeof(int));
+    p.o_meta_l = o; o += align256(2 * (size_t)(B + 1) * sizeof(long long));
+    p.o_S = o; o += align256((size_t)p.total_frames * S_STRIDE * sizeof(float));
+    p.o_ola = o; o += 3 * align256((size_t)p.total_pad * sizeof(float));
+    p.o_tprev = o; if (momentum != 0.f) o += align256((size_t)p.total_frames * NBINS * sizeof(float2));
+    p.o_be = o; o += align256((size_t)B * nblk_of(p.max_wav) * sizeof(double));
+    p.bytes = o;
+    return true;
+}
+}  // namespace
+
+size_t unast_griffinlim_workspace_bytes(const int32_t* frames_host, int B, float momentum) {
+    GlPlan p;
+    if (!frames_host || B <= 0 || !gl_plan(frames_host, B, momentum, p)) return 0;
+    return p.bytes;
+}
+
+int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_host, int B, int n_iter, float momentum,
+                     const float* angles0, float power, int deemphasis, float* wav_out, int32_t* bounds_out,
+                     void* workspace, size_t workspace_bytes, void* stream) {
+    if (!c || !mag_norm || !frames_host || !wav_out || B <= 0 || n_iter < 0) return fail(UNAST_E_ARG, "unast_griffinlim: bad argument");
+    if (momentum < 0.f || momentum >= 1.f) return fail(UNAST_E_ARG, "unast_griffinlim: momentum must be in [0, 1)");
+    GlPlan p;
+    if (!gl_plan(frames_host, B, momentum, p)) return fail(UNAST_E_ARG, "unast_griffinlim: every utterance needs >= 5 frames (librosa reflect padding)");
+    if (!workspace || workspace_bytes < p.bytes) return fail(UNAST_E_WORKSPACE, "unast_griffinlim: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)workspace;
+    int* d_frame_off = (int*)(ws + p.o_meta_i);
+    int* d_step_off = d_frame_off + (B + 1);
+    long long* d_pad_off = (long long*)(ws + p.o_meta_l);
+    long long* d_wav_off = d_pad_off + (B + 1);
+    CU(cudaMemcpyAsync(d_frame_off, p.frame_off.data(), (B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_step_off, p.step_off.data(), (B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_pad_off, p.pad_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_wav_off, p.wav_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    float* S = (float*)(ws + p.o_S);
+    const size_t ola_stride = align256((size_t)p.total_pad * sizeof(float));
+    float* ola[3] = {(float*)(ws + p.o_ola), (float*)(ws + p.o_ola + ola_stride), (float*)(ws + p.o_ola + 2 * ola_stride)};
+    CU(cudaMemsetAsync(ola[0], 0, 3 * ola_stride, st));
+    gl_prepare_kernel<<<c->num_sms * 8, 256, 0, st>>>(mag_norm, p.total_frames, power, S);
+
+    GlParams P;
+    P.S = S; P.frame_off = d_frame_off; P.step_off = d_step_off; P.pad_off = d_pad_off; P.B = B;
+    P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
+    P.angles0 = (const float2*)angles0;
+    P.alpha = momentum / (1.0f + momentum);
+    P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw1024 = c->tw_f; P.wp = c->wp_f; P.phi = c->phi_f;
+    P.wss_per = c->wss_per; P.w2 = c->w2;
+    const int total_steps = p.step_off[B];
+    const int grid = std::min(c->num_sms, total_steps);
+    P.mode = GL_INIT; P.first_iter = 1; P.ola_r = nullptr; P.ola_w = ola[1]; P.ola_z = ola[2];
+    gl_kernel<<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
+    for (int it = 1; it <= n_iter; ++it) {
+        P.mode = GL_ITER; P.first_iter = it == 1;
+        P.ola_r = ola[it % 3]; P.ola_w = ola[(it + 1) % 3]; P.ola_z = ola[(it + 2) % 3];
+        gl_kernel<<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
+    }
+    CU(cudaGetLastError());
+
+    DeemphParams D;
+    D.ola = ola[(n_iter + 1) % 3]; D.x = nullptr; D.frame_off = d_frame_off; D.pad_off = d_pad_off; D.wav_off = d_wav_off;
+    D.out = wav_out; D.wss_per = c->wss_per; D.w2 = c->w2; D.coef = deemphasis ? 0.97 : 0.0;
+    const int chunks = (p.max_wav + DE_CHUNK - 1) / DE_CHUNK;
+    deemph_kernel<<<dim3((chunks + 3) / 4, B), 128, 0, st>>>(D);
+    if (bounds_out) {
+        const int nblk = nblk_of(p.max_wav);
+        double* be = (double*)(ws + p.o_be);
+        block_energy_kernel<<<dim3((nblk + 7) / 8, B), 256, 0, st>>>(wav_out, 0, d_wav_off, B, nblk, be);
+        trim_decide_kernel<<<B, 128, 0, st>>>(wav_out, 0, d_wav_off, nblk, be, bounds_out, c->d_err);
+    }
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+// ---- diagnostics ----
+int unast_debug_rfft(unast_ctx* c, const float* frames, int F, int precision, float* out, void* stream) {
+    if (!c || !frames || !out || F <= 0) return fail(UNAST_E_ARG, "unast_debug_rfft: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (precision == UNAST_PREC_F64)
+        debug_rfft_kernel<double><<<(F + 3) / 4, 128, 4 * xch_elems<double>() * 16, st>>>(frames, F, c->tw_d, c->wp_d, (float2*)out);
+    else
+        debug_rfft_kernel<float><<<(F + 3) / 4, 128, 4 * xch_elems<float>() * 8, st>>>(frames, F, c->tw_f, c->wp_f, (float2*)out);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+int unast_debug_irfft(unast_ctx* c, const float* spec, int F, float* out, void* stream) {
+    if (!c || !spec || !out || F <= 0) return fail(UNAST_E_ARG, "unast_debug_irfft: bad argument");
+    debug_irfft_kernel<<<(F + 3) / 4, 128, 4 * xch_elems<float>() * 8, (cudaStream_t)stream>>>((const float2*)spec, F, c->tw_f, c->wp_f, out);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+}  // extern "C"

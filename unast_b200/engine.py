@@ -1,0 +1,185 @@
+"""Batched device-side interface to the spectral kernels.
+
+torch is used for device memory, streams and (elsewhere) torch.distributed only -- every transform
+is computed by libunast_spectral.so.  ``SpectralEngine`` is what ``utils.get_spectrograms`` /
+``utils.spectrogram2wav`` / ``gl_vocoder.vocode`` / ``prepare_data`` are thin wrappers around; it
+works on whole batches because one utterance cannot fill 148 SMs.
+
+Batch layout (DESIGN.md "data layout in HBM"):
+  wave      1-D float32 or int16 tensor, utterances back to back; ``offsets`` int64 [B+1]
+  bounds    int32 [B, 2]  trim start / end inside each utterance (librosa.effects.trim)
+  frame_off int32 [B+1]   prefix sum of T_b = 1 + (end - start) // 275
+  mag       float32 [sum T, 1025]      utterance b = rows frame_off[b]:frame_off[b+1]
+  mel       float32 [80 * sum T]       utterance b = [80, T_b] block at 80 * frame_off[b]
+            (or [B, T_max, 80] zero padded for the loader path)
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import audio_parameters as ap
+
+HOP, WIN, NBINS, NMELS, NFFT = ap.hop_length, ap.win_length, 1 + ap.n_fft // 2, ap.n_mels, ap.n_fft
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+class SpectralEngine:
+    def __init__(self, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("unast_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.lib = L.load()
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        h = C.c_void_p()
+        L.check(self.lib.unast_create(self.device.index, C.byref(h)))
+        self.h = h
+        self._ws = {}
+        self.num_sms = self.lib.unast_num_sms(self.h)
+        self.launches = 0                      # kernels of ours launched through this engine (bench "gpu_launches")
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                self.lib.unast_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    # -- helpers -------------------------------------------------------------------------------
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _workspace(self, key, nbytes):
+        t = self._ws.get(key)
+        if t is None or t.numel() < nbytes:
+            t = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=self.device)
+            self._ws[key] = t
+        return t
+
+    def check(self):
+        """Synchronise and raise if a kernel flagged a data error (too-short / empty utterance)."""
+        L.check(self.lib.unast_check(self.h, self._stream()))
+
+    def mel_basis(self):
+        out = np.empty((NMELS, NBINS), np.float32)
+        L.check(self.lib.unast_get_mel_basis(self.h, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    @staticmethod
+    def _dtype_code(wave):
+        if wave.dtype == torch.float32:
+            return L.F32
+        if wave.dtype == torch.int16:
+            return L.I16
+        raise TypeError("wave must be float32 or int16, got %s" % wave.dtype)
+
+    # -- forward path ----------------------------------------------------------------------------
+    def trim_bounds(self, wave, offsets, max_len):
+        """librosa.effects.trim bounds for every utterance -> int32 [B, 2] (device)."""
+        B = offsets.numel() - 1
+        bounds = torch.empty((B, 2), dtype=torch.int32, device=self.device)
+        nbytes = self.lib.unast_trim_workspace_bytes(B, int(max_len))
+        ws = self._workspace("trim", nbytes)
+        L.check(self.lib.unast_trim_bounds(self.h, _ptr(wave), self._dtype_code(wave), _ptr(offsets), B, int(max_len),
+                                           _ptr(bounds), _ptr(ws), nbytes, self._stream()))
+        self.launches += 2
+        return bounds
+
+    def frame_offsets(self, bounds):
+        B = bounds.shape[0]
+        fo = torch.empty(B + 1, dtype=torch.int32, device=self.device)
+        L.check(self.lib.unast_frame_offsets(self.h, _ptr(bounds), B, _ptr(fo), self._stream()))
+        self.launches += 1
+        return fo
+
+    def frontend(self, wave, offsets, bounds, frame_off, total_frames, precision="f64", want_mag=True,
+                 mel_layout="per_utt", T_max=0, mel_out=None, mag_out=None):
+        """utils.py:251-276 for a whole batch.  Returns (mel, mag) device tensors (layouts above)."""
+        B = offsets.numel() - 1
+        prec = {"f32": L.PREC_F32, "f64": L.PREC_F64}[precision]
+        if mel_layout == "per_utt":
+            layout = L.MEL_MAJOR_PER_UTT
+            if mel_out is None:
+                mel_out = torch.empty(NMELS * total_frames, dtype=torch.float32, device=self.device)
+        elif mel_layout == "padded":
+            layout = L.MEL_PADDED_BTM
+            if mel_out is None:
+                mel_out = torch.zeros((B, T_max, NMELS), dtype=torch.float32, device=self.device)
+        else:
+            raise ValueError("mel_layout must be 'per_utt' or 'padded'")
+        if want_mag and mag_out is None:
+            mag_out = torch.empty((total_frames, NBINS), dtype=torch.float32, device=self.device)
+        nbytes = self.lib.unast_frontend_workspace_bytes(B)
+        ws = self._workspace("fe", nbytes)
+        L.check(self.lib.unast_frontend(self.h, _ptr(wave), self._dtype_code(wave), _ptr(offsets), _ptr(bounds), _ptr(frame_off),
+                                        B, prec, _ptr(mel_out), layout, int(T_max), _ptr(mag_out if want_mag else None),
+                                        _ptr(ws), nbytes, self._stream()))
+        self.launches += 2
+        return mel_out, (mag_out if want_mag else None)
+
+    # -- inverse path ----------------------------------------------------------------------------
+    def griffinlim(self, mag_norm, frames, n_iter=ap.n_iter, momentum=0.0, angles0=None, power=ap.power,
+                   deemphasis=True, want_trim=True, wav_out=None):
+        """utils.py:289-306 / gl_vocoder.py:17-32 for a batch of normalised magnitude spectrograms.
+
+        mag_norm: float32 [sum T, 1025] device tensor; frames: list of T_b.
+        angles0:  complex64 [sum T, 1025] device tensor (unit phases) or None for the zero-phase start.
+        Returns (wav float32 [sum 275 (T_b-1)], wav_off numpy int64 [B+1], bounds int32 [B,2] device or None).
+        """
+        frames_np = np.ascontiguousarray(np.asarray(frames, dtype=np.int32))
+        B = int(frames_np.size)
+        if mag_norm.dtype != torch.float32 or not mag_norm.is_contiguous():
+            raise TypeError("mag_norm must be a contiguous float32 tensor")
+        if mag_norm.numel() != int(frames_np.sum()) * NBINS:
+            raise ValueError("mag_norm does not match frames")
+        a0 = None
+        if angles0 is not None:
+            if angles0.dtype != torch.complex64 or not angles0.is_contiguous() or angles0.numel() * 1 != int(frames_np.sum()) * NBINS:
+                raise TypeError("angles0 must be a contiguous complex64 [sum T, 1025] tensor")
+            a0 = torch.view_as_real(angles0)
+        fptr = frames_np.ctypes.data_as(C.c_void_p)
+        nbytes = self.lib.unast_griffinlim_workspace_bytes(fptr, B, float(momentum))
+        if nbytes == 0:
+            raise ValueError("every spectrogram needs at least 5 frames (librosa reflect padding)")
+        ws = self._workspace("gl", nbytes)
+        wav_off = np.concatenate([[0], np.cumsum(HOP * (frames_np.astype(np.int64) - 1))])
+        if wav_out is None:
+            wav_out = torch.empty(int(wav_off[-1]), dtype=torch.float32, device=self.device)
+        bounds = torch.empty((B, 2), dtype=torch.int32, device=self.device) if want_trim else None
+        L.check(self.lib.unast_griffinlim(self.h, _ptr(mag_norm), fptr, B, int(n_iter), float(momentum), _ptr(a0), float(power),
+                                          1 if deemphasis else 0, _ptr(wav_out), _ptr(bounds), _ptr(ws), nbytes, self._stream()))
+        self.launches += 3 + int(n_iter) + (2 if want_trim else 0)
+        return wav_out, wav_off, bounds
+
+    # -- diagnostics -------------------------------------------------------------------------------
+    def debug_rfft(self, frames, precision="f32"):
+        F = frames.shape[0]
+        out = torch.empty((F, NBINS), dtype=torch.complex64, device=self.device)
+        L.check(self.lib.unast_debug_rfft(self.h, _ptr(frames), F, {"f32": 0, "f64": 1}[precision],
+                                          _ptr(torch.view_as_real(out)), self._stream()))
+        return out
+
+    def debug_irfft(self, spec):
+        F = spec.shape[0]
+        out = torch.empty((F, WIN), dtype=torch.float32, device=self.device)
+        L.check(self.lib.unast_debug_irfft(self.h, _ptr(torch.view_as_real(spec)), F, _ptr(out), self._stream()))
+        return out
+
+
+_ENGINES = {}
+
+
+def get_engine(device=None):
+    """Process-wide engine per device (tables are built once, like a cuFFT plan)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("unast_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    idx = torch.cuda.current_device() if device is None else int(device)
+    if idx not in _ENGINES:
+        _ENGINES[idx] = SpectralEngine(idx)
+    return _ENGINES[idx]

@@ -114,6 +114,11 @@ int unast_debug_rfft(unast_ctx* ctx, const float* frames, int F, int precision, 
 /* spec: complex64[F][1025]; out: float[F][1102] = first 1102 samples of irfft(spec, 2048). */
 int unast_debug_irfft(unast_ctx* ctx, const float* spec, int F, float* out, void* stream);
 
+/* Sustained FMA issue-rate probe used for the roofline denominators that MEASURED_PEAKS.json lacks:
+ * kind 0 = FFMA (float32), 1 = DFMA (float64), 2 = FFMA2 (packed float32x2).  Launches num_sms*8 CTAs of 256
+ * threads, each thread `iters` x 8 independent FMAs; *flop_out (host) = flop the launch performs; out: float[num_sms*8*256]. */
+int unast_debug_pipe_peak(unast_ctx* ctx, int kind, int iters, float* out, double* flop_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,320 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI (ctypes -> libunast_spectral.so), against the
+CPU oracle on identical seeded inputs.  Tolerances are the north star's:
+  normalised mel / mag: max |d| <= 1e-4 (values in [1e-8, 1]); trim bounds, T and lengths exact;
+  Griffin-Lim: waveform SNR >= 40 dB vs the oracle's output from the same initial phases, spectral
+  convergence within 1e-3 of the oracle's."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import snr_db
+from oracle import spectral_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+GL_SNR_DB = 40.0
+GL_SC_TOL = 1e-3
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _clips(specs):
+    from unast_b200 import synth
+    return [synth.speech_like(d, s) for d, s in specs]
+
+
+# ------------------------------------------------------------------------------------------------
+# FFT core on its own
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("prec,tol", [("f64", 2e-6), ("f32", 5e-4)])
+def test_rfft_core_matches_numpy(engine, prec, tol):
+    torch = _torch()
+    rng = np.random.RandomState(0)
+    F = 37                                                     # ragged vs the 4-frames-per-CTA launch
+    fr = np.zeros((F, 2048), np.float32)
+    fr[:, :1102] = rng.randn(F, 1102).astype(np.float32)
+    ref = np.fft.rfft(fr.astype(np.float64), axis=1)
+    out = engine.debug_rfft(torch.from_numpy(fr).cuda(), prec).cpu().numpy()
+    assert np.abs(out - ref).max() <= tol * np.abs(ref).max()
+    # linearity (size-independent property): rfft(a + 2 b) = rfft(a) + 2 rfft(b)
+    a, b = fr[:16], fr[16:32]
+    lhs = engine.debug_rfft(torch.from_numpy(a + 2 * b).cuda(), prec).cpu().numpy()
+    rhs = out[:16] + 2 * out[16:32]
+    assert np.abs(lhs - rhs).max() <= 4 * tol * np.abs(ref).max()
+
+
+def test_irfft_core_matches_numpy(engine):
+    torch = _torch()
+    rng = np.random.RandomState(1)
+    fr = np.zeros((9, 2048))
+    fr[:, :1102] = rng.randn(9, 1102)
+    spec = np.fft.rfft(fr, axis=1).astype(np.complex64)
+    back = engine.debug_irfft(torch.from_numpy(spec).cuda()).cpu().numpy()
+    ref = np.fft.irfft(spec.astype(np.complex128), axis=1)[:, :1102]
+    assert np.abs(back - ref).max() <= 2e-6 * max(1.0, np.abs(ref).max())
+
+
+def test_mel_basis_equals_oracle(engine):
+    assert np.abs(engine.mel_basis() - so.mel_filterbank()).max() <= 1e-9
+
+
+# ------------------------------------------------------------------------------------------------
+# forward path
+# ------------------------------------------------------------------------------------------------
+def test_frontend_f64_parity_ragged_batch():
+    from unast_b200 import utils as U
+    waves = _clips([(10.0, 0), (3.3, 1), (1.0, 2), (6.57, 3), (2.2, 4)])
+    res = U.spectrograms_from_waves(waves, precision="f64", return_bounds=True)
+    assert len(res) == len(waves)
+    for w, (mel, mag, b) in zip(waves, res):
+        omel, omag, ob = so.spectrograms_from_wave(w, return_bounds=True)
+        assert b == ob                                                           # discrete: exact
+        assert mel.shape == omel.shape and mag.shape == omag.shape
+        assert mel.dtype == np.float32 and mag.dtype == np.float32
+        assert mel.flags.f_contiguous and mag.flags.c_contiguous               # utils.py:275-276 memory order
+        assert np.abs(mag - omag).max() <= TOL
+        assert np.abs(mel - omel).max() <= TOL
+
+
+def test_frontend_f32_fast_mode_error_is_bounded():
+    """The float32 FFT mode is NOT the parity mode: documented bound (DESIGN.md 'precision')."""
+    from unast_b200 import utils as U
+    waves = _clips([(4.0, 20), (2.0, 21)])
+    for w, (mel, mag) in zip(waves, U.spectrograms_from_waves(waves, precision="f32")):
+        omel, omag = so.spectrograms_from_wave(w)
+        d = np.abs(mag - omag)
+        assert d.max() <= 2e-3 and np.quantile(d, 0.999) <= 5e-5
+        assert np.abs(mel - omel).max() <= TOL                                   # mel sums ~25 bins: well inside
+
+
+def test_frontend_matches_reference_golden(golden):
+    from unast_b200 import utils as U
+    for name in ("fwd_a", "fwd_b"):
+        g = golden(name)
+        (mel, mag, b), = U.spectrograms_from_waves([g["pcm"]], return_bounds=True)   # int16 input path
+        assert b == tuple(int(v) for v in g["bounds"])
+        assert mel.shape == g["mel"].shape
+        assert np.abs(mel - g["mel"]).max() <= TOL and np.abs(mag - g["mag"]).max() <= TOL
+
+
+def test_frontend_int16_equals_float_input():
+    from unast_b200 import synth, utils as U
+    w = _clips([(2.5, 30)])[0]
+    q = synth.to_pcm16(w)
+    (mel_i, mag_i), = U.spectrograms_from_waves([q])
+    (mel_f, mag_f), = U.spectrograms_from_waves([q.astype(np.float32) / np.float32(32768.0)])
+    assert np.array_equal(mel_i, mel_f) and np.array_equal(mag_i, mag_f)
+
+
+def test_frontend_without_trim_and_minimum_length():
+    from unast_b200 import utils as U
+    rng = np.random.RandomState(5)
+    waves = [0.1 * rng.randn(n).astype(np.float32) for n in (1025, 1375, 2048, 5000)]
+    res = U.spectrograms_from_waves(waves, do_trim=False)
+    for w, (mel, mag) in zip(waves, res):
+        omel, omag = so.spectrograms_from_wave(w, do_trim=False)
+        assert mel.shape == omel.shape == (1 + w.size // 275, 80)
+        assert np.abs(mag - omag).max() <= TOL and np.abs(mel - omel).max() <= TOL
+
+
+def test_frontend_edge_cases_raise():
+    from unast_b200 import utils as U
+    from unast_b200._lib import UnastError
+    assert U.spectrograms_from_waves([]) == []
+    with pytest.raises(IndexError):
+        U.spectrograms_from_waves([np.zeros(0, np.float32)])                     # utils.py:251 raises on empty audio
+    with pytest.raises(UnastError):
+        U.spectrograms_from_waves([np.ones(600, np.float32)])                    # too short for reflect padding
+
+
+def test_frontend_padded_loader_layout(engine):
+    """[B, T_max, 80] zero-padded batch tensor (collate_fn_transformer, preprocess.py:82-121)."""
+    torch = _torch()
+    waves = _clips([(1.5, 40), (2.5, 41), (1.1, 42)])
+    lens = np.array([w.size for w in waves])
+    off = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)).cuda()
+    wave = torch.from_numpy(np.concatenate(waves)).cuda()
+    bounds = engine.trim_bounds(wave, off, int(lens.max()))
+    fo = engine.frame_offsets(bounds)
+    engine.check()
+    fo_h = fo.cpu().numpy()
+    T_max = int(np.diff(fo_h).max())
+    mel, mag = engine.frontend(wave, off, bounds, fo, int(fo_h[-1]), precision="f64", want_mag=False,
+                               mel_layout="padded", T_max=T_max)
+    assert mag is None and tuple(mel.shape) == (3, T_max, 80)
+    mel = mel.cpu().numpy()
+    for b, w in enumerate(waves):
+        omel, _ = so.spectrograms_from_wave(w)
+        T = omel.shape[0]
+        assert np.abs(mel[b, :T] - omel).max() <= TOL
+        assert np.all(mel[b, T:] == 0)
+
+
+def test_get_spectrograms_drop_in_and_npy_files(tmp_path):
+    from unast_b200 import synth, utils as U
+    from unast_b200.prepare_data import PrepareDataset
+    ids = ["LJ001-0001", "LJ001-0002", "LJ001-0003"]
+    waves = _clips([(1.2, 50), (2.0, 51), (1.6, 52)])
+    for i, w in zip(ids, waves):
+        synth.write_wav_pcm16(str(tmp_path / (i + ".wav")), w)
+    (tmp_path / "metadata.csv").write_text("".join("%s|text|text\n" % i for i in ids))
+    mel, mag = U.get_spectrograms(str(tmp_path / (ids[0] + ".wav")))             # reference signature
+    q = synth.to_pcm16(waves[0]).astype(np.float32) / np.float32(32768.0)
+    omel, omag = so.spectrograms_from_wave(q)
+    assert mel.shape == omel.shape and np.abs(mel - omel).max() <= TOL and np.abs(mag - omag).max() <= TOL
+    with pytest.raises(FileNotFoundError):
+        U.get_spectrograms(str(tmp_path / "nope.wav"))
+    ds = PrepareDataset(str(tmp_path / "metadata.csv"), str(tmp_path))
+    assert len(ds) == 3
+    ds.process([0, 1, 2])
+    for i, w in zip(ids, waves):
+        hdr = open(str(tmp_path / (i + ".pt.npy")), "rb").read(128)
+        assert b"'fortran_order': True" in hdr                                    # same bytes as prepare_data.py:33
+        m, g = np.load(str(tmp_path / (i + ".pt.npy"))), np.load(str(tmp_path / (i + ".mag.npy")))
+        q = synth.to_pcm16(w).astype(np.float32) / np.float32(32768.0)
+        omel, omag = so.spectrograms_from_wave(q)
+        assert m.shape == omel.shape and g.shape == omag.shape
+        assert np.abs(m - omel).max() <= TOL and np.abs(g - omag).max() <= TOL
+
+
+def test_frontend_full_size_batch_properties():
+    """256 LJSpeech-shaped clips (C2 sample): frame counts exact for every clip, values in range,
+    a seeded subset checked against the oracle, and scale invariance: x -> x/2 lowers every unclipped
+    normalised value by exactly 20 log10(2) / 100."""
+    from unast_b200 import synth, utils as U
+    durs = synth.ljspeech_durations(256, seed=1)
+    waves = [synth.speech_like(float(d), 1000 + i) for i, d in enumerate(durs)]
+    res = U.spectrograms_from_waves(waves, return_bounds=True)
+    for w, (mel, mag, b) in zip(waves, res):
+        assert mel.shape[0] == mag.shape[0] == 1 + (b[1] - b[0]) // 275
+        assert mag.min() >= 1e-8 and mag.max() <= 1.0 and np.isfinite(mel).all()
+    for i in np.random.RandomState(0).choice(256, 6, replace=False):
+        omel, omag, ob = so.spectrograms_from_wave(waves[i], return_bounds=True)
+        assert res[i][2] == ob
+        assert np.abs(res[i][0] - omel).max() <= TOL and np.abs(res[i][1] - omag).max() <= TOL
+    half = U.spectrograms_from_waves([w * np.float32(0.5) for w in waves[:8]])
+    for (mel, mag, _), (mel2, mag2) in zip(res[:8], half):
+        inside = (mag > 0.1) & (mag < 0.99)
+        assert np.abs((mag - mag2)[inside] - 0.2 * np.log10(2.0)).max() <= 2e-6
+
+
+# ------------------------------------------------------------------------------------------------
+# inverse path
+# ------------------------------------------------------------------------------------------------
+def _mags(specs):
+    return [so.spectrograms_from_wave(w)[1] for w in _clips(specs)]
+
+
+def _check_gl(y, ref, S):
+    assert y.shape == ref.shape
+    assert snr_db(ref, y) >= GL_SNR_DB
+    assert abs(so.spectral_convergence(y, S) - so.spectral_convergence(ref, S)) <= GL_SC_TOL
+
+
+@pytest.mark.parametrize("iters", [0, 1, 5, 30])
+def test_griffin_lim_classic_zero_phase(iters):
+    from unast_b200 import utils as U
+    mags = _mags([(2.0, 10), (1.2, 11), (3.1, 12)])
+    outs = U.spectrogram2wav_batch(mags, n_iter=iters, do_trim=False)
+    for m, y in zip(mags, outs):
+        ref = so.spectrogram2wav(m, iters=iters, return_untrimmed=True)
+        assert y.dtype == np.float32 and y.size == 275 * (m.shape[0] - 1)
+        _check_gl(y, ref, so.denormalise(m))
+
+
+def test_griffin_lim_classic_100_iterations_seeded_phase():
+    from unast_b200 import utils as U
+    mags = _mags([(1.5, 13), (1.0, 14)])
+    rs = np.random.RandomState(3)
+    a0 = [np.exp(2j * np.pi * rs.rand(1025, m.shape[0])) for m in mags]
+    outs = U.spectrogram2wav_batch(mags, n_iter=100, angles0=[a.T for a in a0], do_trim=False)
+    for m, a, y in zip(mags, a0, outs):
+        ref = so.spectrogram2wav(m, iters=100, angles0=a, return_untrimmed=True)
+        _check_gl(y, ref, so.denormalise(m))
+
+
+def test_griffin_lim_momentum_seeded_phase():
+    """librosa.griffinlim variant of gl_vocoder.py:26 (32 iterations, momentum 0.99) from shared seeded phases."""
+    from unast_b200.gl_vocoder import vocode_arrays
+    mags = _mags([(2.0, 10), (1.2, 11)])
+    rs = np.random.RandomState(3)
+    a0 = [np.exp(2j * np.pi * rs.rand(1025, m.shape[0])) for m in mags]
+    outs = vocode_arrays(mags, n_iter=32, momentum=0.99, angles0=[a.T for a in a0], do_trim=False)
+    for m, a, y in zip(mags, a0, outs):
+        ref = so.vocode_one(m, iters=32, momentum=0.99, angles0=a, return_untrimmed=True).astype(np.float32)
+        _check_gl(y, ref, so.denormalise(m))
+
+
+def test_griffin_lim_matches_reference_golden(golden):
+    from unast_b200 import utils as U
+    from unast_b200.gl_vocoder import vocode_arrays
+    g = golden("gl_classic")
+    y = U.spectrogram2wav(g["mag_in"])                                           # reference signature; ap.n_iter = 60
+    assert y.dtype == np.float32 and y.shape == g["wav"].shape                   # trim bounds equal
+    assert snr_db(g["wav"], y) >= GL_SNR_DB
+    g = golden("gl_fast")
+    np.random.seed(int(g["seed"]))                                               # global RNG, as librosa draws it
+    y, = vocode_arrays([g["mag_in"]])
+    assert y.shape == g["wav"].shape and snr_db(g["wav"], y) >= GL_SNR_DB
+
+
+def test_griffin_lim_trim_and_minimum_frames():
+    from unast_b200 import utils as U
+    mags = _mags([(1.6, 15)])
+    mags.append(np.ascontiguousarray(mags[0][:5]))                               # T = 5 is the smallest legal spectrogram
+    outs = U.spectrogram2wav_batch(mags, n_iter=8)
+    for m, y in zip(mags, outs):
+        ref = so.spectrogram2wav(m, iters=8)
+        assert y.shape == ref.shape                                              # librosa.effects.trim bounds agree
+        assert snr_db(ref, y) >= GL_SNR_DB
+    with pytest.raises(ValueError):
+        U.spectrogram2wav_batch([mags[0][:4]], n_iter=1)
+    with pytest.raises(ValueError):
+        U.spectrogram2wav_batch([np.zeros((8, 80), np.float32)], n_iter=1)
+
+
+def test_invert_spectrogram_and_griffin_lim_raw():
+    """utils.invert_spectrogram (:323-328) and utils.griffin_lim (:309-320) called directly."""
+    from unast_b200 import utils as U
+    w = _clips([(1.3, 16)])[0]
+    X = so.stft(w)
+    y = U.invert_spectrogram(X)
+    ref = so.invert_spectrogram(X)
+    assert y.shape == ref.shape and snr_db(ref, y) >= 100.0
+    S = np.abs(X).astype(np.float32)
+    y = U.griffin_lim(S)                                                          # 60 iterations, zero phase
+    ref = so.griffin_lim(S)
+    _check_gl(y, np.asarray(ref, np.float32), S)
+
+
+def test_stft_istft_round_trip_full_length():
+    """Size-independent property at full size: istft(stft(x)) == x away from the edges (COLA holds for
+    hann 1102 / hop 275 after window-sum normalisation), on a 10 s clip."""
+    from unast_b200 import utils as U
+    w = _clips([(10.0, 17)])[0]
+    X = so.stft(w)                                                                # complex STFT from the oracle ...
+    y = U.invert_spectrogram(X)                                                   # ... inverted on the GPU
+    n = y.size
+    assert n == 275 * (X.shape[1] - 1)
+    assert np.abs(y[2048:n - 2048] - w[2048:n - 2048]).max() <= 2e-5
+
+
+def test_vocode_cli_files(tmp_path):
+    from unast_b200 import gl_vocoder, wavio
+    mags = _mags([(1.2, 18), (1.4, 19)])
+    (tmp_path / "m").mkdir()
+    for i, m in enumerate(mags):
+        np.save(str(tmp_path / "m" / ("utt%d.mag.npy" % i)), m)
+    (tmp_path / "list.csv").write_text("utt0|a|a\nutt1|b|b\n")
+    np.random.seed(11)
+    gl_vocoder.vocode(str(tmp_path / "list.csv"), str(tmp_path / "m"), str(tmp_path / "out"))
+    np.random.seed(11)
+    for i, m in enumerate(mags):
+        y, rate = wavio.read_wav(str(tmp_path / "out" / ("utt%d.wav" % i)))
+        ref = so.vocode_one(m).astype(np.float32)                                 # draws rand(1025, T) in list order
+        assert rate == 22050 and y.shape == ref.shape and snr_db(ref, y) >= GL_SNR_DB

@@ -35,6 +35,7 @@ SYMBOLS = [
     ("unast_griffinlim", _i, [_vp, _vp, _vp, _i, _i, _f, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp]),
     ("unast_debug_rfft", _i, [_vp, _vp, _i, _i, _vp, _vp]),
     ("unast_debug_irfft", _i, [_vp, _vp, _i, _vp, _vp]),
+    ("unast_debug_pipe_peak", _i, [_vp, _i, _i, _vp, C.POINTER(C.c_double), _vp]),
 ]
 
 _lib = None

@@ -146,6 +146,48 @@ __global__ void __launch_bounds__(128) debug_irfft_kernel(const float2* __restri
     });
 }
 
+// Sustained issue rate of one arithmetic pipe: every thread runs ITERS x 8 independent FMAs.
+// kind 0: FFMA (float), 1: DFMA (double), 2: FFMA2 (packed float2, Blackwell fma.rn.f32x2).
+constexpr int PEAK_ILP = 8;
+template <int KIND>
+__global__ void __launch_bounds__(256) pipe_peak_kernel(int iters, float a, float b, float* __restrict__ out) {
+    float acc = 0.f;
+    if constexpr (KIND == 0) {
+        float v[PEAK_ILP];
+#pragma unroll
+        for (int i = 0; i < PEAK_ILP; ++i) v[i] = threadIdx.x + i;
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int i = 0; i < PEAK_ILP; ++i) v[i] = fmaf(v[i], a, b);
+        }
+#pragma unroll
+        for (int i = 0; i < PEAK_ILP; ++i) acc += v[i];
+    } else if constexpr (KIND == 1) {
+        double v[PEAK_ILP];
+        const double da = a, db = b;
+#pragma unroll
+        for (int i = 0; i < PEAK_ILP; ++i) v[i] = threadIdx.x + i;
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int i = 0; i < PEAK_ILP; ++i) v[i] = fma(v[i], da, db);
+        }
+#pragma unroll
+        for (int i = 0; i < PEAK_ILP; ++i) acc += (float)v[i];
+    } else {
+        float2 v[PEAK_ILP];
+        const float2 aa = make_float2(a, a * 1.0001f), bb = make_float2(b, b * 0.999f);
+#pragma unroll
+        for (int i = 0; i < PEAK_ILP; ++i) v[i] = make_float2(threadIdx.x + i, i);
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int i = 0; i < PEAK_ILP; ++i) v[i] = __ffma2_rn(v[i], aa, bb);
+        }
+#pragma unroll
+        for (int i = 0; i < PEAK_ILP; ++i) acc += v[i].x + v[i].y;
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
+
 }  // namespace unast
 
 // ---- C ABI -------------------------------------------------------------------------------------
@@ -448,6 +490,18 @@ int unast_debug_irfft(unast_ctx* c, const float* spec, int F, float* out, void* 
     if (!c || !spec || !out || F <= 0) return fail(UNAST_E_ARG, "unast_debug_irfft: bad argument");
     debug_irfft_kernel<<<(F + 3) / 4, 128, 4 * xch_elems<float>() * 8, (cudaStream_t)stream>>>((const float2*)spec, F, c->tw_f, c->wp_f, out);
     CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+int unast_debug_pipe_peak(unast_ctx* c, int kind, int iters, float* out, double* flop_out, void* stream) {
+    if (!c || !out || iters <= 0 || kind < 0 || kind > 2) return fail(UNAST_E_ARG, "unast_debug_pipe_peak: bad argument");
+    const int grid = c->num_sms * 8, block = 256;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (kind == 0) pipe_peak_kernel<0><<<grid, block, 0, st>>>(iters, 0.999f, 0.001f, out);
+    else if (kind == 1) pipe_peak_kernel<1><<<grid, block, 0, st>>>(iters, 0.999f, 0.001f, out);
+    else pipe_peak_kernel<2><<<grid, block, 0, st>>>(iters, 0.999f, 0.001f, out);
+    CU(cudaGetLastError());
+    if (flop_out) *flop_out = 2.0 * (kind == 2 ? 2.0 : 1.0) * PEAK_ILP * (double)iters * grid * block;
     return UNAST_OK;
 }
 

@@ -1,0 +1,70 @@
+"""torch.distributed plumbing for the multi-GPU runs.
+
+Utterances are independent, so ranks never exchange data on the hot path; torch.distributed is used
+for exactly two things: agreeing on who owns which utterances (deterministic, no communication -- see
+sharding.py) and reducing the per-rank device time / unit counts of a run (max / sum over ranks).
+Backend: NCCL on the GPU box, gloo in the CPU tests.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+
+from .sharding import deal_longest_first, length_buckets
+
+
+def env_world():
+    """(rank, local_rank, world_size) from the torchrun environment (1-process defaults)."""
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
+            int(os.environ.get("WORLD_SIZE", "1")))
+
+
+def init_from_env(backend=None):
+    """Initialise the default process group when launched by torchrun; returns (rank, local_rank, world)."""
+    rank, local_rank, world = env_world()
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    return rank, local_rank, world
+
+
+def _device_for_collectives():
+    if dist.is_initialized() and dist.get_backend() == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+def max_over_ranks(value):
+    """Max of a python float over all ranks (device time of a step: the slowest rank defines it)."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=_device_for_collectives())
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(value):
+    """Sum of a python float over all ranks (units processed by the whole job)."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=_device_for_collectives())
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def barrier():
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.barrier()
+
+
+def my_batches(sizes, rank, world, batch_size):
+    """This rank's utterances (longest-first deal on `sizes`), cut into length-homogeneous batches."""
+    mine = deal_longest_first(sizes, world)[rank]
+    return length_buckets(mine, sizes, batch_size)

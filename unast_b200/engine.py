@@ -172,6 +172,23 @@ class SpectralEngine:
         return out
 
 
+    def pipe_peak_tflops(self, kind="f32", iters=4096, reps=5):
+        """Measured sustained FMA rate (TFLOP/s) of the float32 / float64 / packed-float32x2 pipe (CUDA events)."""
+        k = {"f32": 0, "f64": 1, "f32x2": 2}[kind]
+        out = torch.empty(self.num_sms * 8 * 256, dtype=torch.float32, device=self.device)
+        flop = C.c_double()
+        best = 0.0
+        for r in range(reps + 1):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            L.check(self.lib.unast_debug_pipe_peak(self.h, k, int(iters), _ptr(out), C.byref(flop), self._stream()))
+            e1.record()
+            e1.synchronize()
+            if r:
+                best = max(best, flop.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+        return best
+
+
 _ENGINES = {}
 
 

@@ -132,22 +132,72 @@ __device__ __forceinline__ void warp_fft1024(cplx_t<T> (&v)[32], cplx_t<T>* xch,
     fft32<32>(v);
 }
 
-// Real-FFT post-processing.  in: v[j] = Z[lane + 32 j]; out: v[j] = X[lane + 32 j], nyq = X[1024] (all lanes).
-// wp[k] = (-sin(th)/2, -cos(th)/2), th = 2 pi k / 2048, k = 0..1023.
+// cos(2 pi j / 64), j = 0..16
+constexpr double kCos64[17] = {
+    1.0,
+    0.99518472667219688624483695310948,
+    0.980785280403230449126182236134239,
+    0.95694033573220886493579788698027,
+    0.923879532511286756128183189396788,
+    0.881921264348355029712756863660388,
+    0.831469612302545237078788377617906,
+    0.77301045336273696081090660975847,
+    0.707106781186547524400844362104849,
+    0.634393284163645498215171613225493,
+    0.555570233019602224742830813948533,
+    0.471396736825997648556387625905254,
+    0.382683432365089771728459984030399,
+    0.290284677254462367636192375817395,
+    0.195090322016128267848284868477022,
+    0.0980171403295606019941955638886418,
+    0.0};
+__host__ __device__ constexpr double cos64(int j) { return j <= 16 ? kCos64[j] : -kCos64[32 - j]; }   // j in 0..32
+__host__ __device__ constexpr double sin64(int j) { return j <= 16 ? kCos64[16 - j] : kCos64[j - 16]; }  // j in 0..32
+
+// Source of the real-FFT post-processing factors  wp2[k] = -i W2048^k = (-sin th, -cos th), th = 2 pi k / 2048,
+// for k = lane + 32 j.  Two policies:
+//   WpTable: read the 1024-entry table (shared memory) -- one load per bin, no arithmetic (float32 kernels, which
+//            are issue-bound);
+//   WpLane : wp2[lane + 32 j] = wp2[lane] * W64^j with the per-lane factor in registers and W64^j a compile-time
+//            constant -- four extra FMAs per bin, no memory traffic (float64 kernels, which are bound by the
+//            shared-memory data path).
 template <class T>
-__device__ __forceinline__ void rfft_post(cplx_t<T> (&v)[32], T& nyq, cplx_t<T>* xch, const cplx_t<T>* __restrict__ wp,
-                                          int lane) {
+struct WpTable {
+    const cplx_t<T>* tab;
+    template <int J>
+    __device__ __forceinline__ cplx_t<T> get(int lane) const { return tab[lane + 32 * J]; }
+};
+template <class T>
+struct WpLane {
+    cplx_t<T> b;   // wp2[lane]
+    template <int J>
+    __device__ __forceinline__ cplx_t<T> get(int) const {
+        if constexpr (J == 0) {
+            return b;
+        } else if constexpr (J == 16) {                       // W64^16 = -i
+            return mk(b.y, -b.x);
+        } else {
+            constexpr T c = (T)cos64(J), sn = (T)sin64(J);    // W64^J = c - i sn
+            return mk(fma_t(b.x, c, b.y * sn), fma_t(b.y, c, -(b.x * sn)));
+        }
+    }
+};
+
+// Real-FFT post-processing.  The input frame must have been scaled by 1/2 (folded into the window), i.e.
+// in: v[j] = Z[lane + 32 j] / 2; out: v[j] = X[lane + 32 j], nyq = X[1024] (valid on every lane).
+template <class T, class WP>
+__device__ __forceinline__ void rfft_post(cplx_t<T> (&v)[32], T& nyq, cplx_t<T>* xch, const WP& wp, int lane) {
     using C = cplx_t<T>;
     static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; xch[lane + 32 * j] = v[j]; });
     if (lane == 0) xch[1024] = v[0];
     __syncwarp();
     C z0 = xch[0];
-    nyq = z0.x - z0.y;
+    nyq = (T)2 * (z0.x - z0.y);
     static_for<0, 32>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
         const int k = lane + 32 * j;
-        C z = v[j], p = xch[1024 - k], w = wp[k];
-        T er = (T)0.5 * (z.x + p.x), ei = (T)0.5 * (z.y - p.y);
+        C z = v[j], p = xch[1024 - k], w = wp.template get<j>(lane);
+        T er = z.x + p.x, ei = z.y - p.y;
         T orr = z.x - p.x, oi = z.y + p.y;
         v[j] = mk(fma_t(w.x, orr, fma_t(-w.y, oi, er)), fma_t(w.x, oi, fma_t(w.y, orr, ei)));
     });
@@ -155,10 +205,9 @@ __device__ __forceinline__ void rfft_post(cplx_t<T> (&v)[32], T& nyq, cplx_t<T>*
 }
 
 // Inverse of rfft_post followed by conjugation, i.e. the input of the forward machinery that yields
-// conj(irfft) * 1024.  in: v[j] = X[lane + 32 j], nyq = X[1024]; out: v[j] = conj(Z'[lane + 32 j]).
-template <class T>
-__device__ __forceinline__ void irfft_pre(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* xch, const cplx_t<T>* __restrict__ wp,
-                                          int lane) {
+// conj(irfft) * 2048.  in: v[j] = X[lane + 32 j], nyq = X[1024]; out: v[j] = 2 conj(Z'[lane + 32 j]).
+template <class T, class WP>
+__device__ __forceinline__ void irfft_pre(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* xch, const WP& wp, int lane) {
     using C = cplx_t<T>;
     static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; xch[lane + 32 * j] = v[j]; });
     if (lane == 0) xch[1024] = mk(nyq, (T)0);
@@ -166,10 +215,10 @@ __device__ __forceinline__ void irfft_pre(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* 
     static_for<0, 32>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
         const int k = lane + 32 * j;
-        C x = v[j], p = xch[1024 - k], w = wp[k];
-        T er = (T)0.5 * (x.x + p.x), ei = (T)0.5 * (x.y - p.y);
+        C x = v[j], p = xch[1024 - k], w = wp.template get<j>(lane);
+        T er = x.x + p.x, ei = x.y - p.y;
         T dr = x.x - p.x, di = x.y + p.y;
-        // Z' = (er, ei) + conj(w) * (dr, di);   conj(w) = (w.x, -w.y)
+        // 2 Z' = (er, ei) + conj(w) * (dr, di);   conj(w) = (w.x, -w.y)
         T zr = fma_t(w.x, dr, fma_t(w.y, di, er));
         T zi = fma_t(w.x, di, fma_t(-w.y, dr, ei));
         v[j] = mk(zr, -zi);

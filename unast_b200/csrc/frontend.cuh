@@ -1,62 +1,71 @@
 // K1: fused mel / magnitude front end (replaces reference src/utils.py:251-276).
 //
-// One persistent CTA per SM walks a contiguous range of "steps"; a step is FPS consecutive frames of
-// one utterance.  Per step:
-//   1. all threads stage the step's samples into shared memory (int16/float load, reflect padding of
-//      librosa.stft(center=True), pre-emphasis 0.97 in float32 exactly as numpy rounds it) as two
-//      planes (even / odd sample) so that the packed-complex frame loads are conflict-free;
-//   2. each warp transforms one frame (window -> 32x32 warp FFT -> real post-processing), writes the
-//      dB-normalised magnitude row straight to HBM (coalesced) and leaves |X| in its own exchange
-//      buffer, which doubles as the A operand row of the filterbank contraction;
-//   3. the 1024x80 Slaney filterbank is applied on the tensor cores as a banded 3xTF32
-//      mma.sync.m16n8k8 (only the (k-block, n-tile) pairs that hold non-zeros), then dB-normalised.
-// T = float is the fast mode; T = double reproduces the reference's float64 FFT (numpy.fft) and is
-// the mode that meets the 1e-4 parity gate on every bin (DESIGN.md "precision").
+// One persistent CTA per SM walks a contiguous range of "tiles"; a tile is R = FW * RPW consecutive frames of one
+// utterance.  The CTA is warp-specialised and has no CTA-wide barrier in its steady state:
+//
+//   FW "FFT warps"   each owns RPW frames of the tile and runs them end to end on its own:
+//                    coalesced global loads of the frame's 1102 samples (PCM16 words or float32; the 4x overlap
+//                    between consecutive frames is served by L1/L2), reflect padding of librosa.stft(center=True)
+//                    on the few edge frames, pre-emphasis 0.97 in float32 exactly as numpy rounds it, periodic
+//                    Hann window -> 32x32 warp FFT in registers (one private shared-memory transposition) ->
+//                    real post-processing -> |X|^2; the dB-normalised magnitude row goes straight to HBM with
+//                    coalesced stores, the raw |X| row goes to the tile's row buffer in shared memory.
+//   MW "mel warps"   wait (mbarrier) until every row of the tile is there, apply the 1024x80 Slaney filterbank on
+//                    the tensor cores as a banded 3xTF32 mma.sync.m16n8k8 (only the 149 (k-block, n-tile) pairs
+//                    that hold non-zeros), dB-normalise and store mel, then hand the row buffer back.
+//
+// T = double reproduces the reference's float64 FFT (numpy.fft under librosa.stft) and is the mode that meets the
+// 1e-4 parity gate on every bin; T = float is the fast mode (DESIGN.md "Precision").
 #pragma once
 #include "fft_warp.cuh"
 
 namespace unast {
 
-struct MelPlan {                 // built once on the host (tables.cu), lives in device memory
-    const float4* bfrag;         // [npairs][32] {b0_hi, b1_hi, b0_lo, b1_lo} in mma B-fragment order
+struct MelPlan {                 // built once on the host, lives in device memory
+    const float2* bfrag;         // [npairs][32] {b0, b1} float32 weights in mma B-fragment order
     const int* pair_kb;          // [npairs] k-block (8 bins) of each pair
     int pair_begin[11];          // pairs of n-tile nt are [pair_begin[nt], pair_begin[nt+1])
 };
 
 struct FrontendParams {
-    const void* wave;            // concatenated utterances, float32 or int16
+    const void* wave;            // concatenated utterances, float32 or int16 (4-byte aligned base)
     int wave_is_i16;
     const long long* wave_off;   // [B+1] first sample of each utterance in `wave`
     const int* bounds;           // [B][2] trim start / end relative to the utterance
     const int* frame_off;        // [B+1] prefix sum of T_b
-    const int* step_off;         // [B+1] prefix sum of ceil(T_b / FPS)
+    const int* tile_off;         // [B+1] prefix sum of ceil(T_b / R)
     int B;
     float* mag_out;              // [sum T][1025] or nullptr
     float* mel_out;
     int mel_layout;              // 0: per-utterance mel-major [80][T_b] at 80*frame_off[b]; 1: [B][T_max][80]
     int T_max;
-    const void* win2;            // cplx_t<T>[551]  (w[2n], w[2n+1])
+    const void* win2;            // cplx_t<T>[551]  (w[2n], w[2n+1]) * 0.5 (* 2^-15 for PCM16 input)
     const void* tw1024;          // cplx_t<T>[32*32] W1024^(n1 k1) laid out [k1][n1]
-    const void* wp;              // cplx_t<T>[1024] (-sin/2, -cos/2)
+    const void* wp2;             // cplx_t<T>[1024] (-sin th, -cos th), th = 2 pi k / 2048
     MelPlan mel;
     int* err;
 };
 
-constexpr int A_STRIDE_PAD = 4;  // words of padding between warps' exchange regions (A-row bank spread)
+constexpr int ROW_STRIDE = 1028;         // floats per |X| row: 4 (mod 32) makes the mma A-fragment reads conflict-free
+constexpr int MEL_MAX_PAIRS = 160;
 
-template <class T, int WARPS>
+template <class T, int FW, int RPW, int MW>
 struct FeLayout {
     using C = cplx_t<T>;
-    static constexpr int FPS = WARPS;                                   // frames per step
-    static constexpr int SPAN = HOP * (FPS - 1) + WIN;                  // samples a step touches
-    static constexpr int PLANE = (SPAN + 1) / 2 + 1;
-    static constexpr int XCH_BYTES = xch_elems<T>() * (int)sizeof(C) + A_STRIDE_PAD * 4;
+    static constexpr int R = FW * RPW;                                  // frames per tile (<= 16)
+    static constexpr bool WP_TABLE = sizeof(T) == 4;                    // float: table; double: per-lane factor
+    static constexpr int XCH_BYTES = xch_elems<T>() * (int)sizeof(C);
     static constexpr int off_xch = 0;
-    static constexpr int off_planes = off_xch + WARPS * XCH_BYTES;
-    static constexpr int off_win = (off_planes + 2 * PLANE * 4 + 15) / 16 * 16;
+    static constexpr int off_rows = off_xch + FW * XCH_BYTES;
+    static constexpr int off_win = off_rows + 16 * ROW_STRIDE * 4;
     static constexpr int off_tw = off_win + (NLIVE_C * (int)sizeof(C) + 15) / 16 * 16;
     static constexpr int off_wp = off_tw + 1024 * (int)sizeof(C);
-    static constexpr int bytes = off_wp + 1024 * (int)sizeof(C);
+    static constexpr int off_kb = off_wp + (WP_TABLE ? 1024 * (int)sizeof(C) : 0);
+    static constexpr int off_bar = off_kb + MEL_MAX_PAIRS * 4;
+    static constexpr int off_tmem = off_bar + 2 * 8;
+    static constexpr int bytes = off_tmem + 8;
+    static_assert(R <= 16, "a tile is one m16 MMA tile of frames");
+    static_assert(bytes <= 227 * 1024, "shared memory budget");
 };
 
 __device__ __forceinline__ uint32_t to_tf32(float x) {
@@ -72,10 +81,15 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], 
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-// (20*log10(max(1e-5, m)) - ref_db + max_db) / max_db clipped to [1e-8, 1]  (utils.py:267-272)
+// (20*log10(max(1e-5, m)) - ref_db + max_db) / max_db clipped to [1e-8, 1]  (utils.py:267-272), from m
 __device__ __forceinline__ float db_norm(float m) {
-    float t = 20.0f * (0.30102999566398120f * __log2f(fmaxf(1e-5f, m)));
+    float t = 20.0f * (0.30102999566398120f * lg2_approx(fmaxf(1e-5f, m)));
     t = (t - 20.0f + 100.0f) / 100.0f;
+    return fminf(fmaxf(t, 1e-8f), 1.0f);
+}
+// the same from the power m^2:  20 log10(max(1e-5, m)) = 10 log10(max(1e-10, m^2))
+__device__ __forceinline__ float db_norm_pw(float pw) {
+    const float t = fmaf(0.030102999566398120f, lg2_approx(fmaxf(1e-10f, pw)), 0.8f);
     return fminf(fmaxf(t, 1e-8f), 1.0f);
 }
 
@@ -84,138 +98,282 @@ __device__ __forceinline__ float load_sample(const void* wave, int is_i16, long 
     return reinterpret_cast<const float*>(wave)[idx];
 }
 
-template <class T, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 1) frontend_kernel(const FrontendParams P) {
+// int16 halves of a 32-bit word -> float (exact), without the slow I2F path:
+// bits 0x4B000000 | (s + 32768) is the float 8388608 + s + 32768.
+__device__ __forceinline__ float s16lo_to_f(uint32_t w) {
+    return __uint_as_float((w & 0xffffu) ^ 0x4B008000u) - 8421376.0f;
+}
+__device__ __forceinline__ float s16hi_to_f(uint32_t w) {
+    return __uint_as_float((w >> 16) ^ 0x4B008000u) - 8421376.0f;
+}
+
+// y[n] = x[n] - 0.97 x[n-1] rounded like numpy float32 arithmetic (utils.py:251)
+__device__ __forceinline__ float preemph(float cur, float prev) { return __fsub_rn(cur, __fmul_rn(0.97f, prev)); }
+
+// Loads one frame (window taps only, circularly shifted to start at 0), pre-emphasised and windowed, into
+// v[j] = (y[2n] w[2n], y[2n+1] w[2n+1]),  n = lane + 32 j.
+// wbase: index of the utterance's first (trimmed) sample in `wave`; N: trimmed length; t: frame index.
+// For PCM16 the samples are kept as integer-valued floats: the 2^-15 lives in the window table (exact).
+template <class T, bool I16>
+__device__ __forceinline__ void load_frame(cplx_t<T> (&v)[32], const void* __restrict__ wave, long long wbase, int N, int t,
+                                           const cplx_t<T>* __restrict__ s_win, int lane) {
     using C = cplx_t<T>;
-    using L = FeLayout<T, WARPS>;
-    constexpr int FPS = L::FPS;
-    constexpr int NT = WARPS * 32;
-    extern __shared__ __align__(16) unsigned char smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    C* xch = reinterpret_cast<C*>(smem + L::off_xch + warp * L::XCH_BYTES);
-    float* PE = reinterpret_cast<float*>(smem + L::off_planes);
-    float* PO = PE + L::PLANE;
-    C* s_win = reinterpret_cast<C*>(smem + L::off_win);
-    C* s_tw = reinterpret_cast<C*>(smem + L::off_tw);
-    C* s_wp = reinterpret_cast<C*>(smem + L::off_wp);
-
-    for (int i = tid; i < NLIVE_C; i += NT) s_win[i] = reinterpret_cast<const C*>(P.win2)[i];
-    for (int i = tid; i < 1024; i += NT) {
-        s_tw[i] = reinterpret_cast<const C*>(P.tw1024)[i];
-        s_wp[i] = reinterpret_cast<const C*>(P.wp)[i];
-    }
-
-    const int total_steps = P.step_off[P.B];
-    const int g0 = (int)(((long long)total_steps * blockIdx.x) / gridDim.x);
-    const int g1 = (int)(((long long)total_steps * (blockIdx.x + 1)) / gridDim.x);
-    if (g0 >= g1) return;
-    int b = 0;
-    {   // binary search: last b with step_off[b] <= g0
-        int lo = 0, hi = P.B;
-        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.step_off[mid] <= g0) lo = mid; else hi = mid; }
-        b = lo;
-    }
-    __syncthreads();
-
-    for (int g = g0; g < g1; ++g) {
-        while (g >= P.step_off[b + 1]) ++b;
-        const int ta = (g - P.step_off[b]) * FPS;
-        const int fbase = P.frame_off[b];
-        const int Tb = P.frame_off[b + 1] - fbase;
-        const int nf = min(FPS, Tb - ta);
-        const int s0 = P.bounds[2 * b], N = P.bounds[2 * b + 1] - s0;
-        const long long wbase = P.wave_off[b] + s0;
-        const int p0 = HOP * ta + WIN_LPAD - HALF;       // signal index of the step's first staged sample
-
-        // ---- 1. stage: reflect padding + pre-emphasis, split into even/odd planes ----
-        const int span = HOP * (nf - 1) + WIN;
-        for (int i = tid; i < span; i += NT) {
-            int n = p0 + i;
-            if (n < 0) n = -n; else if (n >= N) n = 2 * (N - 1) - n;
-            float cur = load_sample(P.wave, P.wave_is_i16, wbase + n);
-            float y = cur;
-            if (n > 0) {
-                float prev = load_sample(P.wave, P.wave_is_i16, wbase + n - 1);
-                y = __fsub_rn(cur, __fmul_rn(0.97f, prev));              // utils.py:251, float32 like numpy
+    const int n0 = HOP * t + WIN_LPAD - HALF;                  // signal index of tap 0 (may be negative)
+    const bool interior = (n0 >= 1) && (n0 + WIN + 2 <= N);    // no reflection, x[n0-1] exists, one word of slack
+    if (interior) {
+        if constexpr (I16) {
+            const long long A = wbase + n0 - 1;                // absolute index of the "previous" sample of tap 0
+            const uint32_t* __restrict__ w32 = reinterpret_cast<const uint32_t*>(wave) + (A >> 1) + lane;
+            if (A & 1) {                                       // warp-uniform
+                static_for<0, 18>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    const int n = lane + 32 * j;
+                    if (j < 17 || n < NLIVE_C) {
+                        const uint32_t a = w32[32 * j], b = w32[32 * j + 1];
+                        const float pv = s16hi_to_f(a), e = s16lo_to_f(b), o = s16hi_to_f(b);
+                        const C w = s_win[n];
+                        v[j] = mk((T)preemph(e, pv) * w.x, (T)preemph(o, e) * w.y);
+                    } else {
+                        v[j] = mk((T)0, (T)0);
+                    }
+                });
+            } else {
+                static_for<0, 18>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    const int n = lane + 32 * j;
+                    if (j < 17 || n < NLIVE_C) {
+                        const uint32_t a = w32[32 * j], b = w32[32 * j + 1];
+                        const float pv = s16lo_to_f(a), e = s16hi_to_f(a), o = s16lo_to_f(b);
+                        const C w = s_win[n];
+                        v[j] = mk((T)preemph(e, pv) * w.x, (T)preemph(o, e) * w.y);
+                    } else {
+                        v[j] = mk((T)0, (T)0);
+                    }
+                });
             }
-            if (i & 1) PO[i >> 1] = y; else PE[i >> 1] = y;
-        }
-        __syncthreads();
-
-        // ---- 2. one frame per warp ----
-        float* arow = reinterpret_cast<float*>(xch);
-        if (warp < nf) {
-            const int o = HOP * warp;                    // frame offset inside the staged span
-            const float* pa = (o & 1) ? PO + (o >> 1) : PE + (o >> 1);          // x'[2n]
-            const float* pb = (o & 1) ? PE + ((o + 1) >> 1) : PO + (o >> 1);    // x'[2n+1]
-            C v[32];
+        } else {
+            const float* __restrict__ x = reinterpret_cast<const float*>(wave) + wbase + n0 + 2 * lane;
             static_for<0, 18>([&](auto jj) {
                 constexpr int j = decltype(jj)::value;
                 const int n = lane + 32 * j;
                 if (j < 17 || n < NLIVE_C) {
-                    C w = s_win[n];
-                    v[j] = mk((T)pa[n] * w.x, (T)pb[n] * w.y);
+                    const float pv = x[64 * j - 1], e = x[64 * j], o = x[64 * j + 1];
+                    const C w = s_win[n];
+                    v[j] = mk((T)preemph(e, pv) * w.x, (T)preemph(o, e) * w.y);
                 } else {
                     v[j] = mk((T)0, (T)0);
                 }
             });
-            warp_fft1024<T, 18>(v, xch, s_tw, lane);
-            T nyq;
-            rfft_post<T>(v, nyq, xch, s_wp, lane);
-
-            float* mrow = P.mag_out ? P.mag_out + (size_t)(fbase + ta + warp) * NBINS : nullptr;
-            static_for<0, 32>([&](auto jj) {
-                constexpr int j = decltype(jj)::value;
-                const int k = lane + 32 * j;
-                float re = (float)v[j].x, im = (float)v[j].y;          // complex64 storage of librosa.stft
-                float pw = fmaf(re, re, im * im);
-                float m = pw > 0.0f ? pw * rsqrtf(pw) : 0.0f;           // np.abs
-                arow[k] = m;
-                if (mrow) mrow[k] = db_norm(m);
-            });
-            if (lane == 0 && mrow) mrow[1024] = db_norm(fabsf((float)nyq));
         }
-        __syncthreads();
-
-        // ---- 3. banded 3xTF32 filterbank contraction on the tensor cores (utils.py:263-264) ----
-        for (int nt = warp; nt < NMELS / 8; nt += WARPS) {
-            const int gq = lane >> 2, tq = lane & 3;
-            const float* a_lo = reinterpret_cast<const float*>(smem + L::off_xch + gq * L::XCH_BYTES);
-            const float* a_hi = reinterpret_cast<const float*>(smem + L::off_xch + (gq + 8) * L::XCH_BYTES);
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
-            for (int p = P.mel.pair_begin[nt]; p < P.mel.pair_begin[nt + 1]; ++p) {
-                const int kb = P.mel.pair_kb[p];
-                const float4 bq = P.mel.bfrag[p * 32 + lane];
-                float a[4];
-                a[0] = a_lo[8 * kb + tq];
-                a[2] = a_lo[8 * kb + tq + 4];
-                if (FPS > 8) { a[1] = a_hi[8 * kb + tq]; a[3] = a_hi[8 * kb + tq + 4]; } else { a[1] = 0.f; a[3] = 0.f; }
-                uint32_t ah[4], al[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) { ah[q] = to_tf32(a[q]); al[q] = to_tf32(a[q] - __uint_as_float(ah[q])); }
-                mma_tf32(acc, al, __float_as_uint(bq.x), __float_as_uint(bq.y));
-                mma_tf32(acc, ah, __float_as_uint(bq.z), __float_as_uint(bq.w));
-                mma_tf32(acc, ah, __float_as_uint(bq.x), __float_as_uint(bq.y));
+    } else {
+        // edge frame: reflect padding of librosa.stft(center=True); y[0] = x[0] (np.append(y[0], ...), utils.py:251)
+        auto sample = [&](int m) -> float {                    // pre-emphasised signal at (reflected) index m
+            if (m < 0) m = -m; else if (m >= N) m = 2 * (N - 1) - m;
+            float cur, prev = 0.0f;
+            if constexpr (I16) {
+                const short* s = reinterpret_cast<const short*>(wave) + wbase;
+                cur = (float)s[m];
+                if (m > 0) prev = (float)s[m - 1];
+            } else {
+                const float* s = reinterpret_cast<const float*>(wave) + wbase;
+                cur = s[m];
+                if (m > 0) prev = s[m - 1];
             }
-            const int m0 = 8 * nt + 2 * tq;
+            return m > 0 ? preemph(cur, prev) : cur;
+        };
+        static_for<0, 18>([&](auto jj) {
+            constexpr int j = decltype(jj)::value;
+            const int n = lane + 32 * j;
+            if (j < 17 || n < NLIVE_C) {
+                const C w = s_win[n];
+                v[j] = mk((T)sample(n0 + 2 * n) * w.x, (T)sample(n0 + 2 * n + 1) * w.y);
+            } else {
+                v[j] = mk((T)0, (T)0);
+            }
+        });
+    }
+    static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = mk((T)0, (T)0); });
+}
+
+struct TileInfo {
+    int b, ta, nf, fbase, Tb, N;
+    long long wbase;
+};
+
+// tile g (global tile index) -> utterance / first frame / sizes; `b` is a running lower bound (monotone in g)
+__device__ __forceinline__ TileInfo tile_info(const FrontendParams& P, int g, int& b, int R) {
+    while (g >= P.tile_off[b + 1]) ++b;
+    TileInfo ti;
+    ti.b = b;
+    ti.ta = (g - P.tile_off[b]) * R;
+    ti.fbase = P.frame_off[b];
+    ti.Tb = P.frame_off[b + 1] - ti.fbase;
+    ti.nf = min(R, ti.Tb - ti.ta);
+    const int s0 = P.bounds[2 * b];
+    ti.N = P.bounds[2 * b + 1] - s0;
+    ti.wbase = P.wave_off[b] + s0;
+    return ti;
+}
+
+template <class T, int FW, int RPW, int MW>
+__global__ void __launch_bounds__((FW + MW) * 32, 1) frontend_kernel(const FrontendParams P) {
+    using C = cplx_t<T>;
+    using L = FeLayout<T, FW, RPW, MW>;
+    constexpr int R = L::R;
+    constexpr int NT = (FW + MW) * 32;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* rows = reinterpret_cast<float*>(smem + L::off_rows);
+    C* s_win = reinterpret_cast<C*>(smem + L::off_win);
+    C* s_tw = reinterpret_cast<C*>(smem + L::off_tw);
+    int* s_kb = reinterpret_cast<int*>(smem + L::off_kb);
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + L::off_bar);
+    uint64_t* bar_empty = bar_full + 1;
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::off_tmem);
+
+    const int total_tiles = P.tile_off[P.B];
+    const int g0 = (int)(((long long)total_tiles * blockIdx.x) / gridDim.x);
+    const int g1 = (int)(((long long)total_tiles * (blockIdx.x + 1)) / gridDim.x);
+    if (g0 >= g1) return;
+
+    for (int i = tid; i < NLIVE_C; i += NT) s_win[i] = reinterpret_cast<const C*>(P.win2)[i];
+    for (int i = tid; i < 1024; i += NT) s_tw[i] = reinterpret_cast<const C*>(P.tw1024)[i];
+    if constexpr (L::WP_TABLE) {
+        C* s_wp = reinterpret_cast<C*>(smem + L::off_wp);
+        for (int i = tid; i < 1024; i += NT) s_wp[i] = reinterpret_cast<const C*>(P.wp2)[i];
+    }
+    const int npairs = P.mel.pair_begin[NMELS / 8];
+    for (int i = tid; i < npairs; i += NT) s_kb[i] = P.mel.pair_kb[i];
+    for (int i = tid; i < 16 * ROW_STRIDE; i += NT) rows[i] = 0.0f;      // rows >= R are never written
+    if (tid == 0) {
+        mbar_init(bar_full, FW);
+        mbar_init(bar_empty, MW);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    int b;
+    {   // binary search: last b with tile_off[b] <= g0
+        int lo = 0, hi = P.B;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.tile_off[mid] <= g0) lo = mid; else hi = mid; }
+        b = lo;
+    }
+    if (warp == FW) tmem_alloc(s_tmem, 512);                              // whole tensor memory: one CTA per SM
+    tmem_fence_before_sync();
+    __syncthreads();                                                      // the only CTA-wide barrier
+    tmem_fence_after_sync();
+    const uint32_t tmem = *s_tmem;
+
+    if (warp < FW) {
+        // ================================ FFT warps ================================
+        C* xch = reinterpret_cast<C*>(smem + L::off_xch + warp * L::XCH_BYTES);
+        auto wp = [&]() {
+            if constexpr (L::WP_TABLE) return WpTable<T>{reinterpret_cast<const C*>(smem + L::off_wp)};
+            else return WpLane<T>{reinterpret_cast<const C*>(P.wp2)[lane]};
+        }();
+        for (int g = g0; g < g1; ++g) {
+            const TileInfo ti = tile_info(P, g, b, R);
+            const int it = g - g0;
+#pragma unroll 1
+            for (int r = 0; r < RPW; ++r) {
+                const int f = warp * RPW + r;                            // row of the tile
+                if (f < ti.nf) {
+                    const int t = ti.ta + f;
+                    C v[32];
+                    if (P.wave_is_i16) load_frame<T, true>(v, P.wave, ti.wbase, ti.N, t, s_win, lane);
+                    else load_frame<T, false>(v, P.wave, ti.wbase, ti.N, t, s_win, lane);
+                    warp_fft1024<T, 18>(v, xch, s_tw, lane);
+                    T nyq;
+                    rfft_post<T>(v, nyq, xch, wp, lane);
+                    if (r == 0 && it > 0) mbar_wait(bar_empty, (it - 1) & 1);   // mel warps are done with the previous tile
+                    float* row = rows + f * ROW_STRIDE;
+                    float* mrow = P.mag_out ? P.mag_out + (size_t)(ti.fbase + t) * NBINS : nullptr;
+                    static_for<0, 32>([&](auto jj) {
+                        constexpr int j = decltype(jj)::value;
+                        const int k = lane + 32 * j;
+                        const float re = (float)v[j].x, im = (float)v[j].y;      // complex64 storage of librosa.stft
+                        const float pw = fmaf(re, re, im * im);
+                        row[k] = sqrt_approx(pw);                                 // np.abs
+                        if (mrow) mrow[k] = db_norm_pw(pw);
+                    });
+                    if (lane == 0 && mrow) mrow[1024] = db_norm(fabsf((float)nyq));
+                } else if (r == 0 && it > 0) {
+                    mbar_wait(bar_empty, (it - 1) & 1);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_full);
+        }
+    } else {
+        // ================================ mel warps ================================
+        // The filterbank (B operand) lives in tensor memory: this warp's pairs, in the order it visits them, at
+        // columns 2 lp, 2 lp + 1 of its own 32-lane quadrant -- no shared-memory, L1 or L2 traffic in the tile loop.
+        const int mw = warp - FW;
+        const int gq = lane >> 2, tq = lane & 3;
+        const uint32_t tbase = tmem + ((uint32_t)(32 * (warp & 3)) << 16);
+        {
+            int lp = 0;
+            for (int nt = NMELS / 8 - 1 - mw; nt >= 0; nt -= MW)
+                for (int p = P.mel.pair_begin[nt]; p < P.mel.pair_begin[nt + 1]; ++p, ++lp)
+                    tmem_st2(tbase + 2 * lp, __ldg(P.mel.bfrag + p * 32 + lane));
+            tmem_wait_st();
+        }
+        const float* a_lo = rows + gq * ROW_STRIDE + tq;
+        const float* a_hi = rows + (gq + 8) * ROW_STRIDE + tq;
+        auto pair_mma = [&](float (&acc)[4], int kb, float2 bw) {
+            float a[4];
+            a[0] = a_lo[8 * kb];
+            a[1] = a_hi[8 * kb];
+            a[2] = a_lo[8 * kb + 4];
+            a[3] = a_hi[8 * kb + 4];
+            uint32_t ah[4], al[4];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int f = gq + 8 * h;
-                if (f < nf) {
-                    const float v0 = db_norm(acc[2 * h]), v1 = db_norm(acc[2 * h + 1]);
-                    if (P.mel_layout == 0) {
-                        float* dst = P.mel_out + (size_t)NMELS * fbase + (ta + f);
-                        dst[(size_t)m0 * Tb] = v0;
-                        dst[(size_t)(m0 + 1) * Tb] = v1;
-                    } else {
-                        float* dst = P.mel_out + ((size_t)b * P.T_max + ta + f) * NMELS + m0;
-                        dst[0] = v0;
-                        dst[1] = v1;
+            for (int q = 0; q < 4; ++q) { ah[q] = to_tf32(a[q]); al[q] = to_tf32(a[q] - __uint_as_float(ah[q])); }
+            const uint32_t b0h = to_tf32(bw.x), b1h = to_tf32(bw.y);
+            const uint32_t b0l = to_tf32(bw.x - __uint_as_float(b0h)), b1l = to_tf32(bw.y - __uint_as_float(b1h));
+            mma_tf32(acc, al, b0h, b1h);
+            mma_tf32(acc, ah, b0l, b1l);
+            mma_tf32(acc, ah, b0h, b1h);
+        };
+        for (int g = g0; g < g1; ++g) {
+            const TileInfo ti = tile_info(P, g, b, R);
+            const int it = g - g0;
+            mbar_wait(bar_full, it & 1);
+            // n-tiles are dealt heaviest-first: with MW = 2 warp 0 takes {9, 7, 5, ...}, warp 1 {8, 6, 4, ...}
+            int lp = 0;
+            for (int nt = NMELS / 8 - 1 - mw; nt >= 0; nt -= MW) {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                const int p0 = P.mel.pair_begin[nt], p1 = P.mel.pair_begin[nt + 1];
+                for (int p = p0; p < p1; p += 2) {
+                    const bool two = p + 1 < p1;
+                    float2 bw0 = tmem_ld2(tbase + 2 * lp);
+                    float2 bw1 = tmem_ld2(tbase + 2 * lp + 2);           // harmless over-read on the odd tail
+                    tmem_wait_ld(bw0, bw1);
+                    pair_mma(acc, s_kb[p], bw0);
+                    if (two) pair_mma(acc, s_kb[p + 1], bw1);
+                    lp += two ? 2 : 1;
+                }
+                const int m0 = 8 * nt + 2 * tq;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int f = gq + 8 * h;
+                    if (f < ti.nf) {
+                        const float v0 = db_norm(acc[2 * h]), v1 = db_norm(acc[2 * h + 1]);
+                        if (P.mel_layout == 0) {
+                            float* dst = P.mel_out + (size_t)NMELS * ti.fbase + (ti.ta + f);
+                            dst[(size_t)m0 * ti.Tb] = v0;
+                            dst[(size_t)(m0 + 1) * ti.Tb] = v1;
+                        } else {
+                            float* dst = P.mel_out + ((size_t)ti.b * P.T_max + ti.ta + f) * NMELS + m0;
+                            dst[0] = v0;
+                            dst[1] = v1;
+                        }
                     }
                 }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty);
         }
-        __syncthreads();
+        if constexpr (MW > 1) asm volatile("bar.sync 1, %0;" ::"n"(MW * 32) : "memory");
+        if (warp == FW) tmem_dealloc(tmem, 512);
     }
 }
 

@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_kernel(const GlParams P) 
                     }
                 });
                 warp_fft1024<float, 18>(v, xch, s_tw, lane);
-                rfft_post<float>(v, nyq, xch, s_wp, lane);
+                rfft_post<float>(v, nyq, xch, WpTable<float>{s_wp}, lane);
                 if (P.alpha == 0.0f) {
                     // utils.py:315-316: X = S * est / max(1e-8, |est|)
                     static_for<0, 32>([&](auto jj) {
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_kernel(const GlParams P) 
                 if (a0) pn = cmul(a0[1024], pn);
                 nyq = Srow[1024] * pn.x;                            // ... and of the Nyquist bin
             }
-            irfft_pre<float>(v, nyq, xch, s_wp, lane);
+            irfft_pre<float>(v, nyq, xch, WpTable<float>{s_wp}, lane);
             warp_fft1024<float, 32>(v, xch, s_tw, lane);
             float2* fb = xch;                                        // windowed frame, 1102 floats
             static_for<0, 18>([&](auto jj) {

@@ -13,6 +13,17 @@
 
 using namespace unast;
 
+// Front-end kernel configurations: <arithmetic, FFT warps, frames per FFT warp and tile, mel warps>
+#ifndef UNAST_FE64_FW
+#define UNAST_FE64_FW 7
+#endif
+using FeF32 = FeLayout<float, 14, 1, 2>;
+using FeF64 = FeLayout<double, UNAST_FE64_FW, 2, 1>;
+#define FE_F32_KERNEL frontend_kernel<float, 14, 1, 2>
+#define FE_F64_KERNEL frontend_kernel<double, UNAST_FE64_FW, 2, 1>
+constexpr int FE_F32_THREADS = (14 + 2) * 32;
+constexpr int FE_F64_THREADS = (UNAST_FE64_FW + 1) * 32;
+
 namespace {
 
 thread_local std::string g_err;
@@ -32,15 +43,6 @@ int fail(int code, const std::string& msg) {
 constexpr double kPi = 3.14159265358979323846264338327950288;
 
 size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
-
-float tf32_rna(float x) {
-    uint32_t u;
-    memcpy(&u, &x, 4);
-    u += 0x1000u;
-    u &= 0xffffe000u;
-    memcpy(&x, &u, 4);
-    return x;
-}
 
 // ---- librosa.filters.mel(22050, 2048, 80): Slaney scale, area-normalised, float32 ----
 double hz_to_mel(double f) {
@@ -83,11 +85,12 @@ cudaError_t upload(T** dptr, const std::vector<T>& h) {
 struct unast_ctx {
     int device = 0;
     int num_sms = 0;
-    float2 *win2_f = nullptr, *wini2_f = nullptr, *tw_f = nullptr, *wp_f = nullptr, *phi_f = nullptr;
-    double2 *win2_d = nullptr, *tw_d = nullptr, *wp_d = nullptr;
+    // analysis windows carry the 1/2 of the real-FFT post-processing (and 2^-15 for PCM16 input)
+    float2 *win2_f = nullptr, *win2i_f = nullptr, *wini2_f = nullptr, *tw_f = nullptr, *wp_f = nullptr, *phi_f = nullptr;
+    double2 *win2_d = nullptr, *win2i_d = nullptr, *tw_d = nullptr, *wp_d = nullptr;
     float* wss_per = nullptr;
     double* w2 = nullptr;
-    float4* bfrag = nullptr;
+    float2* bfrag = nullptr;
     int* pair_kb = nullptr;
     int pair_begin[11] = {0};
     int* d_err = nullptr;
@@ -111,11 +114,11 @@ __global__ void __launch_bounds__(128) debug_rfft_kernel(const float* __restrict
     static_for<0, 18>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
         const int n = lane + 32 * j;
-        if (j < 17 || n < NLIVE_C) { float2 s = src[n]; v[j] = mk((T)s.x, (T)s.y); } else v[j] = mk((T)0, (T)0);
+        if (j < 17 || n < NLIVE_C) { float2 s = src[n]; v[j] = mk((T)0.5 * (T)s.x, (T)0.5 * (T)s.y); } else v[j] = mk((T)0, (T)0);
     });
     warp_fft1024<T, 18>(v, xch, tw, lane);
     T nyq;
-    rfft_post<T>(v, nyq, xch, wp, lane);
+    rfft_post<T>(v, nyq, xch, WpTable<T>{wp}, lane);
     float2* dst = out + (size_t)f * NBINS;
     static_for<0, 32>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
@@ -136,13 +139,13 @@ __global__ void __launch_bounds__(128) debug_irfft_kernel(const float2* __restri
     static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = src[lane + 32 * j]; });
     if (lane == 0) v[0].y = 0.f;
     float nyq = src[1024].x;
-    irfft_pre<float>(v, nyq, xch, wp, lane);
+    irfft_pre<float>(v, nyq, xch, WpTable<float>{wp}, lane);
     warp_fft1024<float, 32>(v, xch, tw, lane);
     float2* dst = reinterpret_cast<float2*>(out + (size_t)f * WIN);
     static_for<0, 18>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
         const int n = lane + 32 * j;
-        if (j < 17 || n < NLIVE_C) dst[n] = make_float2(v[j].x * (1.0f / 1024.0f), -v[j].y * (1.0f / 1024.0f));
+        if (j < 17 || n < NLIVE_C) dst[n] = make_float2(v[j].x * (1.0f / 2048.0f), -v[j].y * (1.0f / 2048.0f));
     });
 }
 
@@ -212,12 +215,15 @@ int unast_create(int device, unast_ctx** out) {
 
     std::vector<double> hann(WIN);
     for (int k = 0; k < WIN; ++k) hann[k] = 0.5 - 0.5 * std::cos(2.0 * kPi * k / WIN);
-    std::vector<float2> win2_f(NLIVE_C), wini2_f(NLIVE_C);
-    std::vector<double2> win2_d(NLIVE_C);
+    std::vector<float2> win2_f(NLIVE_C), win2i_f(NLIVE_C), wini2_f(NLIVE_C);
+    std::vector<double2> win2_d(NLIVE_C), win2i_d(NLIVE_C);
     for (int n = 0; n < NLIVE_C; ++n) {
-        win2_d[n] = make_double2(hann[2 * n], hann[2 * n + 1]);
-        win2_f[n] = make_float2((float)hann[2 * n], (float)hann[2 * n + 1]);
-        wini2_f[n] = make_float2((float)(hann[2 * n] / 1024.0), (float)(hann[2 * n + 1] / 1024.0));
+        const double a = hann[2 * n], b = hann[2 * n + 1];
+        win2_d[n] = make_double2(0.5 * a, 0.5 * b);                               // power-of-two scalings are exact
+        win2i_d[n] = make_double2(0.5 * a / 32768.0, 0.5 * b / 32768.0);
+        win2_f[n] = make_float2((float)(0.5 * a), (float)(0.5 * b));
+        win2i_f[n] = make_float2((float)(0.5 * a / 32768.0), (float)(0.5 * b / 32768.0));
+        wini2_f[n] = make_float2((float)(a / 2048.0), (float)(b / 2048.0));
     }
     std::vector<float2> tw_f(1024), wp_f(1024), phi_f(NBINS);
     std::vector<double2> tw_d(1024), wp_d(1024);
@@ -229,8 +235,8 @@ int unast_create(int device, unast_ctx** out) {
         }
     for (int k = 0; k < 1024; ++k) {
         const double th = 2.0 * kPi * k / 2048.0;
-        wp_d[k] = make_double2(-0.5 * std::sin(th), -0.5 * std::cos(th));
-        wp_f[k] = make_float2((float)(-0.5 * std::sin(th)), (float)(-0.5 * std::cos(th)));
+        wp_d[k] = make_double2(-std::sin(th), -std::cos(th));
+        wp_f[k] = make_float2((float)(-std::sin(th)), (float)(-std::cos(th)));
     }
     for (int k = 0; k < NBINS; ++k) {
         const double th = 2.0 * kPi * ((WIN_LPAD * k) % NFFT) / NFFT;
@@ -249,7 +255,7 @@ int unast_create(int device, unast_ctx** out) {
     c->mel_basis = build_mel_basis();
     for (int m = 0; m < NMELS; ++m)
         if (c->mel_basis[(size_t)m * NBINS + 1024] != 0.f) { delete c; return fail(UNAST_E_ARG, "filterbank has weight on the Nyquist bin"); }
-    std::vector<float4> bfrag;
+    std::vector<float2> bfrag;
     std::vector<int> pair_kb;
     for (int nt = 0; nt < NMELS / 8; ++nt) {
         c->pair_begin[nt] = (int)pair_kb.size();
@@ -264,8 +270,7 @@ int unast_create(int device, unast_ctx** out) {
                 const int g = lane >> 2, t = lane & 3;
                 const float b0 = c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t];
                 const float b1 = c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t + 4];
-                const float b0h = tf32_rna(b0), b1h = tf32_rna(b1);
-                bfrag.push_back(make_float4(b0h, b1h, tf32_rna(b0 - b0h), tf32_rna(b1 - b1h)));
+                bfrag.push_back(make_float2(b0, b1));
             }
         }
     }
@@ -273,13 +278,13 @@ int unast_create(int device, unast_ctx** out) {
 
     cudaError_t e = cudaSuccess;
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
-    up(&c->win2_f, win2_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
-    up(&c->win2_d, win2_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
+    up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
+    up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
     up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<float, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeLayout<float, 16>::bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<double, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeLayout<double, 8>::bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F32_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF32::bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F64_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF64::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
@@ -289,12 +294,14 @@ int unast_create(int device, unast_ctx** out) {
 
 int unast_destroy(unast_ctx* c) {
     if (!c) return UNAST_OK;
-    cudaFree(c->win2_f); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
+    cudaFree(c->win2_f); cudaFree(c->win2i_f); cudaFree(c->win2i_d); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
     cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
     cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
     delete c;
     return UNAST_OK;
 }
+
+static int npairs_of(const unast_ctx* c) { return c->pair_begin[NMELS / 8]; }
 
 int unast_num_sms(const unast_ctx* c) { return c ? c->num_sms : 0; }
 
@@ -357,22 +364,24 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
     if (mel_layout == UNAST_MEL_PADDED_BTM && T_max <= 0) return fail(UNAST_E_ARG, "unast_frontend: T_max required for the padded layout");
     if (!workspace || workspace_bytes < unast_frontend_workspace_bytes(B)) return fail(UNAST_E_WORKSPACE, "unast_frontend: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    int* step_off = (int*)workspace;
+    int* tile_off = (int*)workspace;
+    if (npairs_of(c) > MEL_MAX_PAIRS) return fail(UNAST_E_ARG, "unast_frontend: filterbank plan exceeds MEL_MAX_PAIRS");
     FrontendParams P;
     P.wave = wave; P.wave_is_i16 = dtype == UNAST_I16; P.wave_off = (const long long*)wave_off; P.bounds = bounds;
-    P.frame_off = frame_off; P.step_off = step_off; P.B = B; P.mag_out = mag_out; P.mel_out = mel_out;
+    P.frame_off = frame_off; P.tile_off = tile_off; P.B = B; P.mag_out = mag_out; P.mel_out = mel_out;
     P.mel_layout = mel_layout; P.T_max = T_max;
     P.mel.bfrag = c->bfrag; P.mel.pair_kb = c->pair_kb;
     memcpy(P.mel.pair_begin, c->pair_begin, sizeof(P.mel.pair_begin));
     P.err = c->d_err;
+    const bool i16 = dtype == UNAST_I16;
     if (precision == UNAST_PREC_F32) {
-        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, 16, step_off);
-        P.win2 = c->win2_f; P.tw1024 = c->tw_f; P.wp = c->wp_f;
-        frontend_kernel<float, 16><<<c->num_sms, 16 * 32, FeLayout<float, 16>::bytes, st>>>(P);
+        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF32::R, tile_off);
+        P.win2 = i16 ? c->win2i_f : c->win2_f; P.tw1024 = c->tw_f; P.wp2 = c->wp_f;
+        FE_F32_KERNEL<<<c->num_sms, FE_F32_THREADS, FeF32::bytes, st>>>(P);
     } else {
-        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, 8, step_off);
-        P.win2 = c->win2_d; P.tw1024 = c->tw_d; P.wp = c->wp_d;
-        frontend_kernel<double, 8><<<c->num_sms, 8 * 32, FeLayout<double, 8>::bytes, st>>>(P);
+        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF64::R, tile_off);
+        P.win2 = i16 ? (const void*)c->win2i_d : (const void*)c->win2_d; P.tw1024 = c->tw_d; P.wp2 = c->wp_d;
+        FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P);
     }
     CU(cudaGetLastError());
     return UNAST_OK;

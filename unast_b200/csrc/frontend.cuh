@@ -68,15 +68,14 @@ struct FeLayout {
     static_assert(bytes <= 227 * 1024, "shared memory budget");
 };
 
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
+// TF32 operand split for 3xTF32: x = hi + lo with hi = x truncated to 10 mantissa bits (one LOP3) and lo = x - hi
+// (exact).  The tensor core ignores the low 13 bits of a .tf32 operand, so lo can be passed as it is; the error of
+// the three-product sum is ~2^-20 relative.  (cvt.rna.tf32.f32 is emulated with ~5 instructions on sm_100.)
+__device__ __forceinline__ uint32_t tf32_hi(float x) { return __float_as_uint(x) & 0xffffe000u; }
+__device__ __forceinline__ uint32_t tf32_lo(float x, uint32_t hi) { return __float_as_uint(x - __uint_as_float(hi)); }
 
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
         : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
@@ -318,20 +317,20 @@ __global__ void __launch_bounds__((FW + MW) * 32, 1) frontend_kernel(const Front
         }
         const float* a_lo = rows + gq * ROW_STRIDE + tq;
         const float* a_hi = rows + (gq + 8) * ROW_STRIDE + tq;
-        auto pair_mma = [&](float (&acc)[4], int kb, float2 bw) {
+        // operands of one (k-block, n-tile) pair, split for 3xTF32: x = hi + lo with hi = tf32(x), lo = tf32(x - hi)
+        struct PairOps { uint32_t ah[4], al[4], bh[2], bl[2]; };
+        auto pair_ops = [&](int kb, float b0, float b1) {
+            PairOps o;
             float a[4];
             a[0] = a_lo[8 * kb];
             a[1] = a_hi[8 * kb];
             a[2] = a_lo[8 * kb + 4];
             a[3] = a_hi[8 * kb + 4];
-            uint32_t ah[4], al[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) { ah[q] = to_tf32(a[q]); al[q] = to_tf32(a[q] - __uint_as_float(ah[q])); }
-            const uint32_t b0h = to_tf32(bw.x), b1h = to_tf32(bw.y);
-            const uint32_t b0l = to_tf32(bw.x - __uint_as_float(b0h)), b1l = to_tf32(bw.y - __uint_as_float(b1h));
-            mma_tf32(acc, al, b0h, b1h);
-            mma_tf32(acc, ah, b0l, b1l);
-            mma_tf32(acc, ah, b0h, b1h);
+            for (int q = 0; q < 4; ++q) { o.ah[q] = tf32_hi(a[q]); o.al[q] = tf32_lo(a[q], o.ah[q]); }
+            o.bh[0] = tf32_hi(b0); o.bh[1] = tf32_hi(b1);
+            o.bl[0] = tf32_lo(b0, o.bh[0]); o.bl[1] = tf32_lo(b1, o.bh[1]);
+            return o;
         };
         for (int g = g0; g < g1; ++g) {
             const TileInfo ti = tile_info(P, g, b, R);
@@ -340,23 +339,43 @@ __global__ void __launch_bounds__((FW + MW) * 32, 1) frontend_kernel(const Front
             // n-tiles are dealt heaviest-first: with MW = 2 warp 0 takes {9, 7, 5, ...}, warp 1 {8, 6, 4, ...}
             int lp = 0;
             for (int nt = NMELS / 8 - 1 - mw; nt >= 0; nt -= MW) {
-                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                // four independent accumulator sets: consecutive pairs go to different sets and the MMAs are issued
+                // interleaved, so the tensor pipe never waits on its own previous result; summed in a fixed order.
+                float acc[4][4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[u][q] = 0.f;
                 const int p0 = P.mel.pair_begin[nt], p1 = P.mel.pair_begin[nt + 1];
-                for (int p = p0; p < p1; p += 2) {
-                    const bool two = p + 1 < p1;
-                    float2 bw0 = tmem_ld2(tbase + 2 * lp);
-                    float2 bw1 = tmem_ld2(tbase + 2 * lp + 2);           // harmless over-read on the odd tail
-                    tmem_wait_ld(bw0, bw1);
-                    pair_mma(acc, s_kb[p], bw0);
-                    if (two) pair_mma(acc, s_kb[p + 1], bw1);
-                    lp += two ? 2 : 1;
+                int p = p0;
+                for (; p + 4 <= p1; p += 4, lp += 4) {
+                    float4 q0 = tmem_ld4(tbase + 2 * lp), q1 = tmem_ld4(tbase + 2 * lp + 4);
+                    tmem_wait_ld(q0, q1);
+                    PairOps o[4] = {pair_ops(s_kb[p], q0.x, q0.y), pair_ops(s_kb[p + 1], q0.z, q0.w),
+                                    pair_ops(s_kb[p + 2], q1.x, q1.y), pair_ops(s_kb[p + 3], q1.z, q1.w)};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) mma_tf32(acc[u], o[u].al, o[u].bh[0], o[u].bh[1]);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) mma_tf32(acc[u], o[u].ah, o[u].bl[0], o[u].bl[1]);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) mma_tf32(acc[u], o[u].ah, o[u].bh[0], o[u].bh[1]);
                 }
+                for (; p < p1; ++p, ++lp) {                               // tail: <= 3 pairs
+                    float2 bw = tmem_ld2(tbase + 2 * lp), dummy = bw;
+                    tmem_wait_ld(bw, dummy);
+                    const PairOps o = pair_ops(s_kb[p], bw.x, bw.y);
+                    mma_tf32(acc[0], o.al, o.bh[0], o.bh[1]);
+                    mma_tf32(acc[0], o.ah, o.bl[0], o.bl[1]);
+                    mma_tf32(acc[0], o.ah, o.bh[0], o.bh[1]);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[0][q] = (acc[0][q] + acc[1][q]) + (acc[2][q] + acc[3][q]);
                 const int m0 = 8 * nt + 2 * tq;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const int f = gq + 8 * h;
                     if (f < ti.nf) {
-                        const float v0 = db_norm(acc[2 * h]), v1 = db_norm(acc[2 * h + 1]);
+                        const float v0 = db_norm(acc[0][2 * h]), v1 = db_norm(acc[0][2 * h + 1]);
                         if (P.mel_layout == 0) {
                             float* dst = P.mel_out + (size_t)NMELS * ti.fbase + (ti.ta + f);
                             dst[(size_t)m0 * ti.Tb] = v0;

@@ -226,4 +226,115 @@ __device__ __forceinline__ void irfft_pre(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* 
     __syncwarp();
 }
 
+// ---- low-shared-memory variants -------------------------------------------------------------------------
+// warp_fft1024_split transposes the real and the imaginary plane one after the other through a buffer of
+// 32 x XS scalars (float: 4.5 KB, double: 8.5 KB per warp) instead of 32 x XS complex values; the bytes moved are
+// the same.  rfft_post_shfl / irfft_pre_shfl pair bin k with bin 1024 - k by warp shuffles (partner lane
+// (32 - lane) % 32, register 31 - j) instead of a second trip through shared memory; lane 0, whose column pairs
+// with itself (register j <-> 32 - j), goes through a 32-entry side buffer.
+template <class T> struct XsStride;
+template <> struct XsStride<float> { static constexpr int value = 36; };    // 144 B rows: conflict-free 128-bit reads
+template <> struct XsStride<double> { static constexpr int value = 34; };   // 272 B rows
+template <class T> __host__ __device__ constexpr int xs_bytes() { return 32 * XsStride<T>::value * (int)sizeof(T); }
+
+template <class T, int NZ>
+__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const cplx_t<T>* __restrict__ tw, int lane) {
+    using C = cplx_t<T>;
+    constexpr int XS = XsStride<T>::value;
+    fft32<NZ>(v);
+    static_for<1, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; v[k1] = cmul(v[k1], tw[k1 * 32 + lane]); });
+    auto read_row = [&](auto sel) {
+        if constexpr (sizeof(T) == 4) {
+            const float4* row = reinterpret_cast<const float4*>(xs + lane * XS);
+            static_for<0, 8>([&](auto ii) {
+                constexpr int i = decltype(ii)::value;
+                const float4 q = row[i];
+                sel(v[4 * i]) = q.x; sel(v[4 * i + 1]) = q.y; sel(v[4 * i + 2]) = q.z; sel(v[4 * i + 3]) = q.w;
+            });
+        } else {
+            const double2* row = reinterpret_cast<const double2*>(xs + lane * XS);
+            static_for<0, 16>([&](auto ii) {
+                constexpr int i = decltype(ii)::value;
+                const double2 q = row[i];
+                sel(v[2 * i]) = q.x; sel(v[2 * i + 1]) = q.y;
+            });
+        }
+    };
+    static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; xs[k1 * XS + lane] = v[k1].x; });
+    __syncwarp();
+    read_row([](C& c) -> T& { return c.x; });
+    __syncwarp();
+    static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; xs[k1 * XS + lane] = v[k1].y; });
+    __syncwarp();
+    read_row([](C& c) -> T& { return c.y; });
+    __syncwarp();
+    fft32<32>(v);
+}
+
+__device__ __forceinline__ float2 shfl_c(float2 a, int src) {
+    return make_float2(__shfl_sync(0xffffffffu, a.x, src), __shfl_sync(0xffffffffu, a.y, src));
+}
+__device__ __forceinline__ double2 shfl_c(double2 a, int src) {
+    return make_double2(__shfl_sync(0xffffffffu, a.x, src), __shfl_sync(0xffffffffu, a.y, src));
+}
+
+// in: v[j] = Z[lane + 32 j] / 2; out: v[j] = X[lane + 32 j]; nyq = X[1024], valid on lane 0 only.
+// side: 32 complex values of scratch shared memory private to the warp.
+template <class T, class WP>
+__device__ __forceinline__ void rfft_post_shfl(cplx_t<T> (&v)[32], T& nyq, cplx_t<T>* side, const WP& wp, int lane) {
+    using C = cplx_t<T>;
+    const int src = (32 - lane) & 31;
+    const bool l0 = lane == 0;
+    if (l0) static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; side[j] = v[j]; });
+    __syncwarp();
+    nyq = (T)2 * (v[0].x - v[0].y);
+    auto one = [&](C z, C p, C w) {
+        T er = z.x + p.x, ei = z.y - p.y;
+        T orr = z.x - p.x, oi = z.y + p.y;
+        return mk(fma_t(w.x, orr, fma_t(-w.y, oi, er)), fma_t(w.x, oi, fma_t(w.y, orr, ei)));
+    };
+    static_for<0, 16>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        C pa = shfl_c(v[31 - j], src);               // partner of register j
+        C pb = shfl_c(v[j], src);                    // partner of register 31 - j
+        if (l0) { pa = side[(32 - j) & 31]; pb = side[j + 1]; }
+        const C a = one(v[j], pa, wp.template get<j>(lane));
+        const C b = one(v[31 - j], pb, wp.template get<31 - j>(lane));
+        v[j] = a;
+        v[31 - j] = b;
+    });
+    __syncwarp();
+}
+
+// in: v[j] = X[lane + 32 j], nyq = X[1024] (read on lane 0); out: v[j] = 2 conj(Z'[lane + 32 j]).
+template <class T, class WP>
+__device__ __forceinline__ void irfft_pre_shfl(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* side, const WP& wp, int lane) {
+    using C = cplx_t<T>;
+    const int src = (32 - lane) & 31;
+    const bool l0 = lane == 0;
+    if (l0) {
+        side[0] = mk(nyq, (T)0);                     // partner of bin 0 is the Nyquist bin
+        static_for<1, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; side[j] = v[j]; });
+    }
+    __syncwarp();
+    auto one = [&](C x, C p, C w) {
+        T er = x.x + p.x, ei = x.y - p.y;
+        T dr = x.x - p.x, di = x.y + p.y;
+        T zr = fma_t(w.x, dr, fma_t(w.y, di, er));
+        T zi = fma_t(w.x, di, fma_t(-w.y, dr, ei));
+        return mk(zr, -zi);
+    };
+    static_for<0, 16>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        C pa = shfl_c(v[31 - j], src);
+        C pb = shfl_c(v[j], src);
+        if (l0) { pa = side[(32 - j) & 31]; pb = side[j + 1]; }
+        const C a = one(v[j], pa, wp.template get<j>(lane));
+        const C b = one(v[31 - j], pb, wp.template get<31 - j>(lane));
+        v[j] = a;
+        v[31 - j] = b;
+    });
+    __syncwarp();
+}
+
 }  // namespace unast

@@ -82,8 +82,7 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], 
 
 // (20*log10(max(1e-5, m)) - ref_db + max_db) / max_db clipped to [1e-8, 1]  (utils.py:267-272), from m
 __device__ __forceinline__ float db_norm(float m) {
-    float t = 20.0f * (0.30102999566398120f * lg2_approx(fmaxf(1e-5f, m)));
-    t = (t - 20.0f + 100.0f) / 100.0f;
+    const float t = fmaf(0.060205999132796240f, lg2_approx(fmaxf(1e-5f, m)), 0.8f);
     return fminf(fmaxf(t, 1e-8f), 1.0f);
 }
 // the same from the power m^2:  20 log10(max(1e-5, m)) = 10 log10(max(1e-10, m^2))

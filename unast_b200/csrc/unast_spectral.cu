@@ -1,5 +1,7 @@
 // libunast_spectral.so -- host side of the C ABI declared in include/unast_spectral.h:
 // constant tables (built in float64 on the host), launch logic, diagnostics.  No torch types here.
+#include <algorithm>
+#include <cfloat>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -17,10 +19,13 @@ using namespace unast;
 #ifndef UNAST_FE64_FW
 #define UNAST_FE64_FW 7
 #endif
+#ifndef UNAST_FE64_RPW
+#define UNAST_FE64_RPW 2
+#endif
 using FeF32 = FeLayout<float, 14, 1, 2>;
-using FeF64 = FeLayout<double, UNAST_FE64_FW, 2, 1>;
+using FeF64 = FeLayout<double, UNAST_FE64_FW, UNAST_FE64_RPW, 1>;
 #define FE_F32_KERNEL frontend_kernel<float, 14, 1, 2>
-#define FE_F64_KERNEL frontend_kernel<double, UNAST_FE64_FW, 2, 1>
+#define FE_F64_KERNEL frontend_kernel<double, UNAST_FE64_FW, UNAST_FE64_RPW, 1>
 constexpr int FE_F32_THREADS = (14 + 2) * 32;
 constexpr int FE_F64_THREADS = (UNAST_FE64_FW + 1) * 32;
 
@@ -88,7 +93,8 @@ struct unast_ctx {
     // analysis windows carry the 1/2 of the real-FFT post-processing (and 2^-15 for PCM16 input)
     float2 *win2_f = nullptr, *win2i_f = nullptr, *wini2_f = nullptr, *tw_f = nullptr, *wp_f = nullptr, *phi_f = nullptr;
     double2 *win2_d = nullptr, *win2i_d = nullptr, *tw_d = nullptr, *wp_d = nullptr;
-    float* wss_per = nullptr;
+    float *wss_per = nullptr, *rinv_l = nullptr, *rinv_r = nullptr;
+    float2* wa2_f = nullptr;
     double* w2 = nullptr;
     float2* bfrag = nullptr;
     int* pair_kb = nullptr;
@@ -116,9 +122,15 @@ __global__ void __launch_bounds__(128) debug_rfft_kernel(const float* __restrict
         const int n = lane + 32 * j;
         if (j < 17 || n < NLIVE_C) { float2 s = src[n]; v[j] = mk((T)0.5 * (T)s.x, (T)0.5 * (T)s.y); } else v[j] = mk((T)0, (T)0);
     });
-    warp_fft1024<T, 18>(v, xch, tw, lane);
     T nyq;
-    rfft_post<T>(v, nyq, xch, WpTable<T>{wp}, lane);
+    if constexpr (sizeof(T) == 4) {          // float: the low-shared-memory core the Griffin-Lim kernel uses
+        warp_fft1024_split<T, 18>(v, reinterpret_cast<T*>(xch), tw, lane);
+        rfft_post_shfl<T>(v, nyq, reinterpret_cast<C*>(reinterpret_cast<unsigned char*>(xch) + xs_bytes<T>()), WpTable<T>{wp}, lane);
+        nyq = __shfl_sync(0xffffffffu, nyq, 0);
+    } else {                                 // double: the core of the front-end kernel
+        warp_fft1024<T, 18>(v, xch, tw, lane);
+        rfft_post<T>(v, nyq, xch, WpTable<T>{wp}, lane);
+    }
     float2* dst = out + (size_t)f * NBINS;
     static_for<0, 32>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
@@ -139,8 +151,8 @@ __global__ void __launch_bounds__(128) debug_irfft_kernel(const float2* __restri
     static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = src[lane + 32 * j]; });
     if (lane == 0) v[0].y = 0.f;
     float nyq = src[1024].x;
-    irfft_pre<float>(v, nyq, xch, WpTable<float>{wp}, lane);
-    warp_fft1024<float, 32>(v, xch, tw, lane);
+    irfft_pre_shfl<float>(v, nyq, reinterpret_cast<float2*>(reinterpret_cast<unsigned char*>(xch) + xs_bytes<float>()), WpTable<float>{wp}, lane);
+    warp_fft1024_split<float, 32>(v, reinterpret_cast<float*>(xch), tw, lane);
     float2* dst = reinterpret_cast<float2*>(out + (size_t)f * WIN);
     static_for<0, 18>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
@@ -251,6 +263,26 @@ int unast_create(int device, unast_ctx** out) {
         for (int m = mmax; m >= 0; --m) acc = (float)((double)acc + w2[r + HOP * m]);   // ascending frame index
         wss_per[r] = acc;
     }
+    // Griffin-Lim load tables: interior frames multiply by analysis window / envelope in one go; edge frames look the
+    // reciprocal envelope up by padded position (left edge) or by offset from the last frame's first tap (right edge).
+    auto wss_host = [&](int q, int T) -> float {                   // librosa.filters.window_sumsquare at padded position q
+        const int c = q - WIN_LPAD;
+        if (c < 0) return 0.f;
+        const int t_hi = std::min(T - 1, c / HOP);
+        const int t_lo = c < WIN ? 0 : (c - WIN) / HOP + 1;
+        float acc = 0.f;
+        for (int t = t_lo; t <= t_hi; ++t) acc = (float)((double)acc + w2[c - HOP * t]);
+        return acc;
+    };
+    auto rinv_of = [](float w) -> float { return w > FLT_MIN ? (float)(1.0 / (double)w) : 1.0f; };
+    std::vector<float2> wa2_f(NLIVE_C);
+    for (int n = 0; n < NLIVE_C; ++n)
+        wa2_f[n] = make_float2((float)(0.5 * hann[2 * n] / (double)wss_per[(2 * n) % HOP]),
+                               (float)(0.5 * hann[2 * n + 1] / (double)wss_per[(2 * n + 1) % HOP]));
+    const int T_big = 64;
+    std::vector<float> rinv_l(GL_EDGE_L), rinv_r(GL_EDGE_R);
+    for (int q = 0; q < GL_EDGE_L; ++q) rinv_l[q] = rinv_of(wss_host(q, T_big));
+    for (int u = 0; u < GL_EDGE_R; ++u) rinv_r[u] = rinv_of(wss_host(u - 1100 + WIN_LPAD + HOP * (T_big - 1), T_big));
 
     c->mel_basis = build_mel_basis();
     for (int m = 0; m < NMELS; ++m)
@@ -280,12 +312,14 @@ int unast_create(int device, unast_ctx** out) {
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
     up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
     up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
+    up(&c->wa2_f, wa2_f); up(&c->rinv_l, rinv_l); up(&c->rinv_r, rinv_r);
     up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F32_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF32::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F64_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF64::bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
     *out = c;
@@ -296,6 +330,7 @@ int unast_destroy(unast_ctx* c) {
     if (!c) return UNAST_OK;
     cudaFree(c->win2_f); cudaFree(c->win2i_f); cudaFree(c->win2i_d); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
     cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
+    cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
     cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
     delete c;
     return UNAST_OK;
@@ -390,19 +425,18 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
 // ---- Griffin-Lim ----
 namespace {
 struct GlPlan {
-    std::vector<int> frame_off, step_off;
+    std::vector<int> frame_off;
     std::vector<long long> pad_off, wav_off;
     long long total_frames = 0, total_pad = 0, total_wav = 0;
     int max_wav = 0;
     size_t o_meta_i = 0, o_meta_l = 0, o_S = 0, o_ola = 0, o_tprev = 0, o_be = 0, bytes = 0;
 };
 bool gl_plan(const int32_t* frames, int B, float momentum, GlPlan& p) {
-    p.frame_off.assign(B + 1, 0); p.step_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.wav_off.assign(B + 1, 0);
+    p.frame_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.wav_off.assign(B + 1, 0);
     for (int b = 0; b < B; ++b) {
         const int T = frames[b];
         if (T < 5) return false;                                    // reflect padding of the in-loop stft needs 275 (T-1) > 1024
         p.frame_off[b + 1] = p.frame_off[b] + T;
-        p.step_off[b + 1] = p.step_off[b] + (T + GL_FPS - 1) / GL_FPS;
         p.pad_off[b + 1] = p.pad_off[b] + NFFT + (long long)HOP * (T - 1);
         p.wav_off[b + 1] = p.wav_off[b] + (long long)HOP * (T - 1);
         p.max_wav = std::max(p.max_wav, HOP * (T - 1));
@@ -437,11 +471,9 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     cudaStream_t st = (cudaStream_t)stream;
     char* ws = (char*)workspace;
     int* d_frame_off = (int*)(ws + p.o_meta_i);
-    int* d_step_off = d_frame_off + (B + 1);
     long long* d_pad_off = (long long*)(ws + p.o_meta_l);
     long long* d_wav_off = d_pad_off + (B + 1);
     CU(cudaMemcpyAsync(d_frame_off, p.frame_off.data(), (B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(d_step_off, p.step_off.data(), (B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d_pad_off, p.pad_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d_wav_off, p.wav_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
     float* S = (float*)(ws + p.o_S);
@@ -451,20 +483,24 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     gl_prepare_kernel<<<c->num_sms * 8, 256, 0, st>>>(mag_norm, p.total_frames, power, S);
 
     GlParams P;
-    P.S = S; P.frame_off = d_frame_off; P.step_off = d_step_off; P.pad_off = d_pad_off; P.B = B;
+    P.S = S; P.frame_off = d_frame_off; P.pad_off = d_pad_off; P.B = B; P.total_frames = (int)p.total_frames;
     P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
     P.angles0 = (const float2*)angles0;
     P.alpha = momentum / (1.0f + momentum);
-    P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw1024 = c->tw_f; P.wp = c->wp_f; P.phi = c->phi_f;
-    P.wss_per = c->wss_per; P.w2 = c->w2;
-    const int total_steps = p.step_off[B];
-    const int grid = std::min(c->num_sms, total_steps);
+    P.wa2 = c->wa2_f; P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw1024 = c->tw_f; P.wp2 = c->wp_f; P.phi = c->phi_f;
+    P.rinv_l = c->rinv_l; P.rinv_r = c->rinv_r; P.wss_per = c->wss_per; P.w2 = c->w2;
+    // one run of frames per warp; keep runs >= 8 frames so that seams (atomics) stay a small share
+    const int grid = (int)std::max<long long>(1, std::min<long long>(c->num_sms, p.total_frames / (8 * GL_WARPS)));
+    auto launch = [&]() {
+        if (momentum != 0.f) gl_kernel<true><<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
+        else gl_kernel<false><<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
+    };
     P.mode = GL_INIT; P.first_iter = 1; P.ola_r = nullptr; P.ola_w = ola[1]; P.ola_z = ola[2];
-    gl_kernel<<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
+    launch();
     for (int it = 1; it <= n_iter; ++it) {
         P.mode = GL_ITER; P.first_iter = it == 1;
         P.ola_r = ola[it % 3]; P.ola_w = ola[(it + 1) % 3]; P.ola_z = ola[(it + 2) % 3];
-        gl_kernel<<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
+        launch();
     }
     CU(cudaGetLastError());
 

@@ -114,7 +114,7 @@ __device__ __forceinline__ float preemph(float cur, float prev) { return __fsub_
 // For PCM16 the samples are kept as integer-valued floats: the 2^-15 lives in the window table (exact).
 template <class T, bool I16>
 __device__ __forceinline__ void load_frame(cplx_t<T> (&v)[32], const void* __restrict__ wave, long long wbase, int N, int t,
-                                           const cplx_t<T>* __restrict__ s_win, int lane) {
+                                           const cplx_t<T>* __restrict__ s_win, float* scratch, int lane) {
     using C = cplx_t<T>;
     const int n0 = HOP * t + WIN_LPAD - HALF;                  // signal index of tap 0 (may be negative)
     const bool interior = (n0 >= 1) && (n0 + WIN + 2 <= N);    // no reflection, x[n0-1] exists, one word of slack
@@ -179,16 +179,23 @@ __device__ __forceinline__ void load_frame(cplx_t<T> (&v)[32], const void* __res
             }
             return m > 0 ? preemph(cur, prev) : cur;
         };
+        // compact runtime loop (edge frames are rare; unrolling this path 36x bloats the instruction cache): stage the
+        // taps in the warp's idle exchange buffer, then pick them up with static register indices
+#pragma unroll 4
+        for (int i = lane; i < WIN; i += 32) scratch[i] = sample(n0 + i);
+        __syncwarp();
         static_for<0, 18>([&](auto jj) {
             constexpr int j = decltype(jj)::value;
             const int n = lane + 32 * j;
             if (j < 17 || n < NLIVE_C) {
                 const C w = s_win[n];
-                v[j] = mk((T)sample(n0 + 2 * n) * w.x, (T)sample(n0 + 2 * n + 1) * w.y);
+                const float2 y = reinterpret_cast<const float2*>(scratch)[n];
+                v[j] = mk((T)y.x * w.x, (T)y.y * w.y);
             } else {
                 v[j] = mk((T)0, (T)0);
             }
         });
+        __syncwarp();
     }
     static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = mk((T)0, (T)0); });
 }
@@ -276,8 +283,8 @@ __global__ void __launch_bounds__((FW + MW) * 32, 1) frontend_kernel(const Front
                 if (f < ti.nf) {
                     const int t = ti.ta + f;
                     C v[32];
-                    if (P.wave_is_i16) load_frame<T, true>(v, P.wave, ti.wbase, ti.N, t, s_win, lane);
-                    else load_frame<T, false>(v, P.wave, ti.wbase, ti.N, t, s_win, lane);
+                    if (P.wave_is_i16) load_frame<T, true>(v, P.wave, ti.wbase, ti.N, t, s_win, reinterpret_cast<float*>(xch), lane);
+                    else load_frame<T, false>(v, P.wave, ti.wbase, ti.N, t, s_win, reinterpret_cast<float*>(xch), lane);
                     warp_fft1024<T, 18>(v, xch, s_tw, lane);
                     T nyq;
                     rfft_post<T>(v, nyq, xch, wp, lane);

@@ -144,31 +144,45 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_kernel(const GlParams P) 
                     }
                 });
             } else {
+                // Edge frame (rare): a compact runtime loop stages the normalised, reflect-padded taps in the idle
+                // transposition buffer (unrolling this path 36x would bloat the instruction cache); the loop body is
+                // branch-free so that the unrolled loads are issued back to back.
                 const float* __restrict__ src = P.ola_r + ubase;
-                auto sample = [&](int i) -> float {                      // tap i of the frame, normalised
-                    int n = HOP * t + WIN_LPAD + i - HALF;
-                    if (n < 0) n = -n; else if (n >= L) n = 2 * (L - 1) - n;
-                    const int q = n + HALF;
-                    float y = src[q];
-                    if (Tb >= GL_TABLE_MIN_T) {
-                        const int u = q - WIN_LPAD - HOP * (Tb - 1) + 1100;
-                        y *= (t < 4) ? P.rinv_l[q] : P.rinv_r[u];
-                    } else {
-                        const float w = wss_at(q, Tb, P.wss_per, P.w2);
-                        if (w > FLT_MIN) y = y / w;                       // librosa.istft: y[nz] /= wss[nz]
+                const int nbase = HOP * t + WIN_LPAD - HALF;
+                if (Tb >= GL_TABLE_MIN_T) {
+                    const float* __restrict__ rtab = (t < 4) ? P.rinv_l : P.rinv_r + (1100 - WIN_LPAD - HOP * (Tb - 1));
+#pragma unroll 6
+                    for (int i = lane; i < WIN; i += 32) {
+                        int n = abs(nbase + i);                            // reflect at 0
+                        n = min(n, 2 * (L - 1) - n);                       // reflect at L - 1
+                        const int q = n + HALF;
+                        xs[i] = src[q] * rtab[q];
                     }
-                    return y;
-                };
+                } else {
+#pragma unroll 1
+                    for (int i = lane; i < WIN; i += 32) {
+                        int n = abs(nbase + i);
+                        n = min(n, 2 * (L - 1) - n);
+                        const int q = n + HALF;
+                        float y = src[q];
+                        const float w = wss_at(q, Tb, P.wss_per, P.w2);
+                        if (w > FLT_MIN) y = y / w;                         // librosa.istft: y[nz] /= wss[nz]
+                        xs[i] = y;
+                    }
+                }
+                __syncwarp();
                 static_for<0, 18>([&](auto jj) {
                     constexpr int j = decltype(jj)::value;
                     const int n = lane + 32 * j;
                     if (j < 17 || n < NLIVE_C) {
                         const float2 w = s_win[n];
-                        v[j] = make_float2(sample(2 * n) * w.x, sample(2 * n + 1) * w.y);
+                        const float2 y = reinterpret_cast<const float2*>(xs)[n];
+                        v[j] = make_float2(y.x * w.x, y.y * w.y);
                     } else {
                         v[j] = make_float2(0.f, 0.f);
                     }
                 });
+                __syncwarp();
             }
             static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = make_float2(0.f, 0.f); });
             // ---- 2. STFT column ----

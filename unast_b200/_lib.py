@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libunast_spectral.so")
+LIB_PATH = os.environ.get("UNAST_SPECTRAL_LIB") or os.path.join(_HERE, "libunast_spectral.so")   # override: A/B builds
 
 OK, E_CUDA, E_ARG, E_WORKSPACE, E_DATA = 0, -1, -2, -3, -4
 F32, I16 = 0, 1

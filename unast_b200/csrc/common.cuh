@@ -55,7 +55,7 @@ __device__ __forceinline__ float2 cadd(float2 a, float2 b) {
 }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) {
 #if UNAST_PACKED_F32
-    return __fadd2_rn(a, make_float2(-b.x, -b.y));
+    return __ffma2_rn(b, make_float2(-1.0f, -1.0f), a);      // a - b in one packed instruction (exact: b * -1 is exact)
 #else
     return make_float2(a.x - b.x, a.y - b.y);
 #endif

@@ -39,6 +39,7 @@ struct GlParams {
     const long long* pad_off;    // [B+1] prefix sum of Lp_b = 2048 + 275 (T_b - 1)
     int B;
     int total_frames;
+    const long long* cost_off;   // [B+1] prefix sum of the utterances' cost (interior frame 4, edge frame 5): run partition
     const float* ola_r;          // read buffer  (unused in GL_INIT)
     float* ola_w;                // write buffer
     float* ola_z;                // buffer whose seams are zeroed for the next iteration
@@ -91,9 +92,23 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_kernel(const GlParams P) 
     for (int i = tid; i < 1024; i += NT) { s_tw[i] = P.tw1024[i]; s_wp[i] = P.wp2[i]; }
     __syncthreads();                                                    // the only CTA-wide barrier
 
-    // this warp's run of frames
+    // this warp's run of frames: equal shares of the total cost (edge frames are ~1.3x an interior frame)
     const long long W = (long long)gridDim.x * GL_WARPS, wid = (long long)blockIdx.x * GL_WARPS + warp;
-    const int f0 = (int)((P.total_frames * wid) / W), f1 = (int)((P.total_frames * (wid + 1)) / W);
+    const long long total_cost = P.cost_off[P.B];
+    auto frame_at = [&](long long c) -> int {                          // frame that contains cost point c
+        if (c <= 0) return 0;
+        if (c >= total_cost) return P.total_frames;
+        int lo = 0, hi = P.B;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.cost_off[mid] <= c) lo = mid; else hi = mid; }
+        const int T = P.frame_off[lo + 1] - P.frame_off[lo];
+        int ci = (int)(c - P.cost_off[lo]), t;
+        const int head = 5 * min(4, T), inner = 4 * max(0, T - 8);
+        if (ci < head) t = ci / 5;
+        else if (ci < head + inner) t = 4 + (ci - head) / 4;
+        else t = 4 + max(0, T - 8) + (ci - head - inner) / 5;
+        return P.frame_off[lo] + min(t, T - 1);
+    };
+    const int f0 = frame_at((total_cost * wid) / W), f1 = frame_at((total_cost * (wid + 1)) / W);
     if (f0 >= f1) return;
     int b;
     {

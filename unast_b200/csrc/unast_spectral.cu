@@ -426,25 +426,26 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
 namespace {
 struct GlPlan {
     std::vector<int> frame_off;
-    std::vector<long long> pad_off, wav_off;
+    std::vector<long long> pad_off, wav_off, cost_off;
     long long total_frames = 0, total_pad = 0, total_wav = 0;
     int max_wav = 0;
     size_t o_meta_i = 0, o_meta_l = 0, o_S = 0, o_ola = 0, o_tprev = 0, o_be = 0, bytes = 0;
 };
 bool gl_plan(const int32_t* frames, int B, float momentum, GlPlan& p) {
-    p.frame_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.wav_off.assign(B + 1, 0);
+    p.frame_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.wav_off.assign(B + 1, 0); p.cost_off.assign(B + 1, 0);
     for (int b = 0; b < B; ++b) {
         const int T = frames[b];
         if (T < 5) return false;                                    // reflect padding of the in-loop stft needs 275 (T-1) > 1024
         p.frame_off[b + 1] = p.frame_off[b] + T;
         p.pad_off[b + 1] = p.pad_off[b] + NFFT + (long long)HOP * (T - 1);
         p.wav_off[b + 1] = p.wav_off[b] + (long long)HOP * (T - 1);
+        p.cost_off[b + 1] = p.cost_off[b] + 4LL * T + std::min(T, 8);          // interior frame 4, edge frame 5 (gl_kernel)
         p.max_wav = std::max(p.max_wav, HOP * (T - 1));
     }
     p.total_frames = p.frame_off[B]; p.total_pad = p.pad_off[B]; p.total_wav = p.wav_off[B];
     size_t o = 0;
     p.o_meta_i = o; o += align256(2 * (size_t)(B + 1) * sizeof(int));
-    p.o_meta_l = o; o += align256(2 * (size_t)(B + 1) * sizeof(long long));
+    p.o_meta_l = o; o += align256(3 * (size_t)(B + 1) * sizeof(long long));
     p.o_S = o; o += align256((size_t)p.total_frames * S_STRIDE * sizeof(float));
     p.o_ola = o; o += 3 * align256((size_t)p.total_pad * sizeof(float));
     p.o_tprev = o; if (momentum != 0.f) o += align256((size_t)p.total_frames * NBINS * sizeof(float2));
@@ -473,9 +474,11 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     int* d_frame_off = (int*)(ws + p.o_meta_i);
     long long* d_pad_off = (long long*)(ws + p.o_meta_l);
     long long* d_wav_off = d_pad_off + (B + 1);
+    long long* d_cost_off = d_wav_off + (B + 1);
     CU(cudaMemcpyAsync(d_frame_off, p.frame_off.data(), (B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d_pad_off, p.pad_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d_wav_off, p.wav_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_cost_off, p.cost_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
     float* S = (float*)(ws + p.o_S);
     const size_t ola_stride = align256((size_t)p.total_pad * sizeof(float));
     float* ola[3] = {(float*)(ws + p.o_ola), (float*)(ws + p.o_ola + ola_stride), (float*)(ws + p.o_ola + 2 * ola_stride)};
@@ -483,7 +486,7 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     gl_prepare_kernel<<<c->num_sms * 8, 256, 0, st>>>(mag_norm, p.total_frames, power, S);
 
     GlParams P;
-    P.S = S; P.frame_off = d_frame_off; P.pad_off = d_pad_off; P.B = B; P.total_frames = (int)p.total_frames;
+    P.S = S; P.frame_off = d_frame_off; P.pad_off = d_pad_off; P.B = B; P.total_frames = (int)p.total_frames; P.cost_off = d_cost_off;
     P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
     P.angles0 = (const float2*)angles0;
     P.alpha = momentum / (1.0f + momentum);

@@ -221,6 +221,18 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(precision, frames):
+    """DRAM bytes (read + write) of one front-end launch from the committed `ncu --set full` capture
+    (profiles/roofline_traffic.json), scaled per frame to this launch; None if no capture is recorded."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        with open(p) as fh:
+            rec = json.load(fh)["frontend_" + precision]
+        return rec["dram_bytes"] / rec["frames"] * frames
+    except Exception:
+        return None
+
+
 def run_ours(args):
     import torch
     from unast_b200 import dist as D
@@ -305,7 +317,8 @@ def run_ours(args):
     bytes_per_frame = 275 * 2 + NBINS * 4 + NMELS * 4
     achieved = my_frames * bytes_per_frame / (fe_kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                "traffic": None, "kernel": "frontend_kernel<%s>" % ("double,8" if args.precision == "f64" else "float,16"),
+                "traffic": ncu_traffic(args.precision, my_frames),
+                "kernel": "frontend_kernel<%s>" % ("double,7,2,1" if args.precision == "f64" else "float,14,1,2"),
                 "kernel_ms": fe_kernel_ms, "frames_per_launch": my_frames, "bytes_per_frame": bytes_per_frame,
                 "peak_source": peak_src,
                 "fft_tflops": my_frames * FFT_FLOP / (fe_kernel_ms * 1e-3) / 1e12}

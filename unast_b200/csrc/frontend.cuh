@@ -402,4 +402,209 @@ __global__ void __launch_bounds__((FW + MW) * 32, 1) frontend_kernel(const Front
     }
 }
 
+// dB-normalise and store one 16-frame x 8-mel accumulator tile (mma C-fragment layout) in the requested layout
+__device__ __forceinline__ void store_mel_tile(const FrontendParams& P, const TileInfo& ti, int nt, const float (&s4)[4], int gq, int tq) {
+    const int m0 = 8 * nt + 2 * tq;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int f = gq + 8 * h;
+        if (f < ti.nf) {
+            const float v0 = db_norm(s4[2 * h]), v1 = db_norm(s4[2 * h + 1]);
+            if (P.mel_layout == 0) {
+                float* dst = P.mel_out + (size_t)NMELS * ti.fbase + (ti.ta + f);
+                dst[(size_t)m0 * ti.Tb] = v0;
+                dst[(size_t)(m0 + 1) * ti.Tb] = v1;
+            } else {
+                float* dst = P.mel_out + ((size_t)ti.b * P.T_max + ti.ta + f) * NMELS + m0;
+                dst[0] = v0;
+                dst[1] = v1;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Cooperative variant: every warp is an FFT warp (balanced over the four SM sub-partitions, the whole FP64 pipe is
+// used) and the tile's filterbank contraction is shared by all warps between two CTA barriers:
+//     [each warp: RPW frames -> rows] -> barrier -> [each warp: its mel units on the tensor cores] -> barrier
+// A mel unit is an n-tile (8 mels) or half of one; halves accumulate into a small shared tile with red.shared.add
+// (exactly two contributions onto zero: order-independent) that a designated warp finalises after the second
+// barrier.  B fragments live in tensor memory: warp w keeps the pairs of its units, in visiting order, at columns
+// [128 (w / 4), ...) of quadrant w % 4.
+struct MelUnit { int nt, p0, p1, split; };        // pairs [p0, p1) of n-tile nt; split = index of the shared tile or -1
+
+struct MelCoop {                                   // built on the host for a given warp count
+    const MelUnit* units;                          // [unit_begin[FW]]
+    int unit_begin[17];                            // units of warp w are [unit_begin[w], unit_begin[w + 1])
+    int nsplit;                                    // number of split n-tiles (<= 4)
+    int split_nt[4];                               // their n-tile
+};
+
+constexpr int MEL_MAX_UNITS = 32;
+
+template <class T, int FW, int RPW>
+struct FeCoopLayout {
+    using C = cplx_t<T>;
+    static constexpr int R = FW * RPW;
+    static constexpr bool WP_TABLE = sizeof(T) == 4;
+    static constexpr int XCH_BYTES = xch_elems<T>() * (int)sizeof(C);
+    static constexpr int off_xch = 0;
+    static constexpr int off_rows = off_xch + FW * XCH_BYTES;
+    static constexpr int off_win = off_rows + 16 * ROW_STRIDE * 4;
+    static constexpr int off_tw = off_win + (NLIVE_C * (int)sizeof(C) + 15) / 16 * 16;
+    static constexpr int off_wp = off_tw + 1024 * (int)sizeof(C);
+    static constexpr int off_kb = off_wp + (WP_TABLE ? 1024 * (int)sizeof(C) : 0);
+    static constexpr int off_units = off_kb + MEL_MAX_PAIRS * 4;
+    static constexpr int off_part = off_units + MEL_MAX_UNITS * 16;
+    static constexpr int off_tmem = off_part + 4 * 128 * 4;
+    static constexpr int bytes = off_tmem + 16;
+    static_assert(R == 16, "a tile is one m16 MMA tile of frames");
+    static_assert(bytes <= 227 * 1024, "shared memory budget");
+};
+
+template <class T, int FW, int RPW>
+__global__ void __launch_bounds__(FW * 32, 1) frontend_coop_kernel(const FrontendParams P, const MelCoop M) {
+    using C = cplx_t<T>;
+    using L = FeCoopLayout<T, FW, RPW>;
+    constexpr int R = L::R;
+    constexpr int NT = FW * 32;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* rows = reinterpret_cast<float*>(smem + L::off_rows);
+    C* s_win = reinterpret_cast<C*>(smem + L::off_win);
+    C* s_tw = reinterpret_cast<C*>(smem + L::off_tw);
+    int* s_kb = reinterpret_cast<int*>(smem + L::off_kb);
+    MelUnit* s_units = reinterpret_cast<MelUnit*>(smem + L::off_units);
+    float* part = reinterpret_cast<float*>(smem + L::off_part);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::off_tmem);
+
+    const int total_tiles = P.tile_off[P.B];
+    const int g0 = (int)(((long long)total_tiles * blockIdx.x) / gridDim.x);
+    const int g1 = (int)(((long long)total_tiles * (blockIdx.x + 1)) / gridDim.x);
+    if (g0 >= g1) return;
+
+    for (int i = tid; i < NLIVE_C; i += NT) s_win[i] = reinterpret_cast<const C*>(P.win2)[i];
+    for (int i = tid; i < 1024; i += NT) s_tw[i] = reinterpret_cast<const C*>(P.tw1024)[i];
+    if constexpr (L::WP_TABLE) {
+        C* s_wp = reinterpret_cast<C*>(smem + L::off_wp);
+        for (int i = tid; i < 1024; i += NT) s_wp[i] = reinterpret_cast<const C*>(P.wp2)[i];
+    }
+    const int npairs = P.mel.pair_begin[NMELS / 8];
+    for (int i = tid; i < npairs; i += NT) s_kb[i] = P.mel.pair_kb[i];
+    for (int i = tid; i < M.unit_begin[FW]; i += NT) s_units[i] = M.units[i];
+    for (int i = tid; i < 4 * 128; i += NT) part[i] = 0.0f;
+    if (warp == 0) tmem_alloc(s_tmem, 512);                               // whole tensor memory: one CTA per SM
+    int b;
+    {   // binary search: last b with tile_off[b] <= g0
+        int lo = 0, hi = P.B;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.tile_off[mid] <= g0) lo = mid; else hi = mid; }
+        b = lo;
+    }
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    const uint32_t tbase = *s_tmem + ((uint32_t)(32 * (warp & 3)) << 16) + 128u * (uint32_t)(warp >> 2);   // <= 64 pairs per warp
+    const int u0 = M.unit_begin[warp], u1 = M.unit_begin[warp + 1];
+    {   // this warp's B fragments -> tensor memory, in visiting order
+        int lp = 0;
+        for (int u = u0; u < u1; ++u)
+            for (int p = s_units[u].p0; p < s_units[u].p1; ++p, ++lp)
+                tmem_st2(tbase + 2 * lp, __ldg(P.mel.bfrag + p * 32 + lane));
+        tmem_wait_st();
+    }
+
+    C* xch = reinterpret_cast<C*>(smem + L::off_xch + warp * L::XCH_BYTES);
+    auto wp = [&]() {
+        if constexpr (L::WP_TABLE) return WpTable<T>{reinterpret_cast<const C*>(smem + L::off_wp)};
+        else return WpLane<T>{reinterpret_cast<const C*>(P.wp2)[lane]};
+    }();
+    const int gq = lane >> 2, tq = lane & 3;
+    const float* a_lo = rows + gq * ROW_STRIDE + tq;
+    const float* a_hi = rows + (gq + 8) * ROW_STRIDE + tq;
+
+    for (int g = g0; g < g1; ++g) {
+        const TileInfo ti = tile_info(P, g, b, R);
+        // ---------------- phase 1: this warp's frames ----------------
+#pragma unroll 1
+        for (int r = 0; r < RPW; ++r) {
+            const int f = warp * RPW + r;
+            if (f < ti.nf) {
+                const int t = ti.ta + f;
+                C v[32];
+                if (P.wave_is_i16) load_frame<T, true>(v, P.wave, ti.wbase, ti.N, t, s_win, reinterpret_cast<float*>(xch), lane);
+                else load_frame<T, false>(v, P.wave, ti.wbase, ti.N, t, s_win, reinterpret_cast<float*>(xch), lane);
+                warp_fft1024<T, 18>(v, xch, s_tw, lane);
+                T nyq;
+                rfft_post<T>(v, nyq, xch, wp, lane);
+                float* row = rows + f * ROW_STRIDE;
+                float* mrow = P.mag_out ? P.mag_out + (size_t)(ti.fbase + t) * NBINS : nullptr;
+                static_for<0, 32>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    const int k = lane + 32 * j;
+                    const float re = (float)v[j].x, im = (float)v[j].y;      // complex64 storage of librosa.stft
+                    const float pw = fmaf(re, re, im * im);
+                    row[k] = sqrt_approx(pw);                                 // np.abs
+                    if (mrow) mrow[k] = db_norm_pw(pw);
+                });
+                if (lane == 0 && mrow) mrow[1024] = db_norm(fabsf((float)nyq));
+            }
+        }
+        __syncthreads();                                                  // rows of the tile complete
+        // ---------------- phase 2: this warp's mel units (3xTF32 mma.sync, banded) ----------------
+        int lp = 0;
+        for (int u = u0; u < u1; ++u) {
+            const MelUnit un = s_units[u];
+            float acc[4][4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[a][q] = 0.f;
+            auto pair_ops = [&](int kb, float b0, float b1, float (&d)[4], int pass) {
+                float a[4] = {a_lo[8 * kb], a_hi[8 * kb], a_lo[8 * kb + 4], a_hi[8 * kb + 4]};
+                uint32_t ah[4], al[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { ah[q] = tf32_hi(a[q]); al[q] = tf32_lo(a[q], ah[q]); }
+                const uint32_t b0h = tf32_hi(b0), b1h = tf32_hi(b1);
+                (void)pass;
+                mma_tf32(d, al, b0h, b1h);
+                mma_tf32(d, ah, tf32_lo(b0, b0h), tf32_lo(b1, b1h));
+                mma_tf32(d, ah, b0h, b1h);
+            };
+            int p = un.p0;
+            for (; p + 4 <= un.p1; p += 4, lp += 4) {
+                float4 q0 = tmem_ld4(tbase + 2 * lp), q1 = tmem_ld4(tbase + 2 * lp + 4);
+                tmem_wait_ld(q0, q1);
+                pair_ops(s_kb[p], q0.x, q0.y, acc[0], 0);
+                pair_ops(s_kb[p + 1], q0.z, q0.w, acc[1], 0);
+                pair_ops(s_kb[p + 2], q1.x, q1.y, acc[2], 0);
+                pair_ops(s_kb[p + 3], q1.z, q1.w, acc[3], 0);
+            }
+            for (; p < un.p1; ++p, ++lp) {
+                float2 bw = tmem_ld2(tbase + 2 * lp), dummy = bw;
+                tmem_wait_ld(bw, dummy);
+                pair_ops(s_kb[p], bw.x, bw.y, acc[0], 0);
+            }
+            float s4[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) s4[q] = (acc[0][q] + acc[1][q]) + (acc[2][q] + acc[3][q]);
+            if (un.split >= 0) {
+                float* dst = part + un.split * 128 + lane * 4;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) atomicAdd(dst + q, s4[q]);
+            } else {
+                store_mel_tile(P, ti, un.nt, s4, gq, tq);
+            }
+        }
+        __syncthreads();                                                  // rows free again, split tiles complete
+        if (warp < M.nsplit) {
+            float* src = part + warp * 128 + lane * 4;
+            float s4[4] = {src[0], src[1], src[2], src[3]};
+            src[0] = src[1] = src[2] = src[3] = 0.0f;
+            store_mel_tile(P, ti, M.split_nt[warp], s4, gq, tq);
+        }
+    }
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(*s_tmem, 512);
+}
+
 }  // namespace unast

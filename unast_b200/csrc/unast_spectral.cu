@@ -15,19 +15,32 @@
 
 using namespace unast;
 
-// Front-end kernel configurations: <arithmetic, FFT warps, frames per FFT warp and tile, mel warps>
+// Front-end kernel configurations.  Default: the cooperative kernel (every warp an FFT warp, mel phase shared by all
+// warps); -DUNAST_FE_SPECIALISED=1 selects the warp-specialised variant (dedicated mel warps) for A/B runs.
+#ifndef UNAST_FE_SPECIALISED
+#define UNAST_FE_SPECIALISED 0
+#endif
 #ifndef UNAST_FE64_FW
 #define UNAST_FE64_FW 7
 #endif
 #ifndef UNAST_FE64_RPW
 #define UNAST_FE64_RPW 2
 #endif
+#if UNAST_FE_SPECIALISED
 using FeF32 = FeLayout<float, 14, 1, 2>;
 using FeF64 = FeLayout<double, UNAST_FE64_FW, UNAST_FE64_RPW, 1>;
 #define FE_F32_KERNEL frontend_kernel<float, 14, 1, 2>
 #define FE_F64_KERNEL frontend_kernel<double, UNAST_FE64_FW, UNAST_FE64_RPW, 1>
 constexpr int FE_F32_THREADS = (14 + 2) * 32;
 constexpr int FE_F64_THREADS = (UNAST_FE64_FW + 1) * 32;
+#else
+using FeF32 = FeCoopLayout<float, 16, 1>;
+using FeF64 = FeCoopLayout<double, 8, 2>;
+#define FE_F32_KERNEL frontend_coop_kernel<float, 16, 1>
+#define FE_F64_KERNEL frontend_coop_kernel<double, 8, 2>
+constexpr int FE_F32_THREADS = 16 * 32;
+constexpr int FE_F64_THREADS = 8 * 32;
+#endif
 
 namespace {
 
@@ -99,6 +112,8 @@ struct unast_ctx {
     float2* bfrag = nullptr;
     int* pair_kb = nullptr;
     int pair_begin[11] = {0};
+    MelUnit* units8 = nullptr; MelUnit* units16 = nullptr;   // cooperative mel phase: unit lists for 8 / 16 warps
+    MelCoop coop8, coop16;
     int* d_err = nullptr;
     std::vector<float> mel_basis;
 };
@@ -307,11 +322,51 @@ int unast_create(int device, unast_ctx** out) {
         }
     }
     c->pair_begin[NMELS / 8] = (int)pair_kb.size();
+    // Cooperative mel phase: n-tiles (split in two halves when clearly above the per-warp share) dealt to the warps
+    // longest-first; a warp's units are stored contiguously in the order it visits them.
+    std::vector<MelUnit> h_units8, h_units16;
+    auto build_coop = [&](int FW, std::vector<MelUnit>& out, MelCoop& mc) {
+        const int total = c->pair_begin[NMELS / 8];
+        const double share = (double)total / FW;
+        std::vector<MelUnit> items;
+        mc.nsplit = 0;
+        std::vector<int> order(NMELS / 8);
+        for (int nt = 0; nt < NMELS / 8; ++nt) order[nt] = nt;
+        std::sort(order.begin(), order.end(), [&](int a, int b) {
+            return (c->pair_begin[a + 1] - c->pair_begin[a]) > (c->pair_begin[b + 1] - c->pair_begin[b]); });
+        for (int nt : order) {                                         // largest first: they get the (at most 4) splits
+            const int p0 = c->pair_begin[nt], p1 = c->pair_begin[nt + 1], n = p1 - p0;
+            if (n > 1.15 * share && mc.nsplit < 4) {
+                const int mid = p0 + (n + 1) / 2;
+                items.push_back({nt, p0, mid, mc.nsplit});
+                items.push_back({nt, mid, p1, mc.nsplit});
+                mc.split_nt[mc.nsplit++] = nt;
+            } else {
+                items.push_back({nt, p0, p1, -1});
+            }
+        }
+        std::sort(items.begin(), items.end(), [](const MelUnit& a, const MelUnit& b) { return (a.p1 - a.p0) > (b.p1 - b.p0); });
+        std::vector<std::vector<MelUnit>> per(FW);
+        std::vector<int> load(FW, 0);
+        for (const MelUnit& it : items) {
+            int w = 0;
+            for (int k = 1; k < FW; ++k) if (load[k] < load[w]) w = k;
+            per[w].push_back(it);
+            load[w] += it.p1 - it.p0;
+        }
+        out.clear();
+        for (int w = 0; w < FW; ++w) { mc.unit_begin[w] = (int)out.size(); for (const MelUnit& it : per[w]) out.push_back(it); }
+        for (int w = FW; w <= 16; ++w) mc.unit_begin[w] = (int)out.size();
+        for (int k = mc.nsplit; k < 4; ++k) mc.split_nt[k] = 0;
+    };
+    build_coop(8, h_units8, c->coop8);
+    build_coop(16, h_units16, c->coop16);
 
     cudaError_t e = cudaSuccess;
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
     up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
     up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
+    up(&c->units8, h_units8); up(&c->units16, h_units16);
     up(&c->wa2_f, wa2_f); up(&c->rinv_l, rinv_l); up(&c->rinv_r, rinv_r);
     up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
@@ -322,6 +377,8 @@ int unast_create(int device, unast_ctx** out) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
+    c->coop8.units = c->units8; c->coop16.units = c->units16;
+    if ((int)h_units8.size() > MEL_MAX_UNITS || (int)h_units16.size() > MEL_MAX_UNITS) { unast_destroy(c); return fail(UNAST_E_ARG, "unast_create: mel unit table too large"); }
     *out = c;
     return UNAST_OK;
 }
@@ -330,6 +387,7 @@ int unast_destroy(unast_ctx* c) {
     if (!c) return UNAST_OK;
     cudaFree(c->win2_f); cudaFree(c->win2i_f); cudaFree(c->win2i_d); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
     cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
+    cudaFree(c->units8); cudaFree(c->units16);
     cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
     cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
     delete c;
@@ -412,11 +470,19 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
     if (precision == UNAST_PREC_F32) {
         step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF32::R, tile_off);
         P.win2 = i16 ? c->win2i_f : c->win2_f; P.tw1024 = c->tw_f; P.wp2 = c->wp_f;
+#if UNAST_FE_SPECIALISED
         FE_F32_KERNEL<<<c->num_sms, FE_F32_THREADS, FeF32::bytes, st>>>(P);
+#else
+        FE_F32_KERNEL<<<c->num_sms, FE_F32_THREADS, FeF32::bytes, st>>>(P, c->coop16);
+#endif
     } else {
         step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF64::R, tile_off);
         P.win2 = i16 ? (const void*)c->win2i_d : (const void*)c->win2_d; P.tw1024 = c->tw_d; P.wp2 = c->wp_d;
+#if UNAST_FE_SPECIALISED
         FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P);
+#else
+        FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P, c->coop8);
+#endif
     }
     CU(cudaGetLastError());
     return UNAST_OK;

@@ -318,3 +318,44 @@ def test_vocode_cli_files(tmp_path):
         y, rate = wavio.read_wav(str(tmp_path / "out" / ("utt%d.wav" % i)))
         ref = so.vocode_one(m).astype(np.float32)                                 # draws rand(1025, T) in list order
         assert rate == 22050 and y.shape == ref.shape and snr_db(ref, y) >= GL_SNR_DB
+
+
+# ------------------------------------------------------------------------------------------------
+# structure-specific edge cases of the kernels (tile / run boundaries, short utterances)
+# ------------------------------------------------------------------------------------------------
+def test_frontend_tile_boundaries_ragged_frame_counts():
+    """Frame counts around multiples of the 16-frame tile (15, 16, 17, 31, 32, 33 frames) and a batch large enough
+    that several CTAs share an utterance: every frame must land in the right row."""
+    from unast_b200 import utils as U
+    rng = np.random.RandomState(7)
+    lens = [275 * (t - 1) + int(rng.randint(0, 275)) for t in (15, 16, 17, 31, 32, 33, 5, 48)]
+    waves = [0.2 * rng.randn(n).astype(np.float32) for n in lens]
+    res = U.spectrograms_from_waves(waves, do_trim=False)
+    for w, (mel, mag) in zip(waves, res):
+        omel, omag = so.spectrograms_from_wave(w, do_trim=False)
+        assert mel.shape == omel.shape and mag.shape == omag.shape
+        assert np.abs(mag - omag).max() <= TOL and np.abs(mel - omel).max() <= TOL
+
+
+def test_griffin_lim_run_seams_and_short_utterances():
+    """Griffin-Lim on a batch that mixes very short spectrograms (5..13 frames: exact edge envelope, runs shorter
+    than the 827-sample overlap) with a long one (every warp's run has seams on both sides)."""
+    from unast_b200 import utils as U
+    long_mag = _mags([(6.0, 60)])[0]
+    mags = [np.ascontiguousarray(long_mag[40:40 + t]) for t in (5, 6, 7, 8, 11, 12, 13)] + [long_mag]
+    outs = U.spectrogram2wav_batch(mags, n_iter=12, do_trim=False)
+    for m, y in zip(mags, outs):
+        ref = so.spectrogram2wav(m, iters=12, return_untrimmed=True)
+        _check_gl(y, ref, so.denormalise(m))
+    # the same long spectrogram alone (small grid: runs of ~8 frames) gives the same waveform as inside the batch
+    alone = U.spectrogram2wav_batch([long_mag], n_iter=12, do_trim=False)[0]
+    assert snr_db(outs[-1], alone) >= 80.0
+
+
+def test_griffin_lim_is_deterministic():
+    from unast_b200 import utils as U
+    mags = _mags([(3.0, 61), (1.0, 62)])
+    a = U.spectrogram2wav_batch(mags, n_iter=10, do_trim=False)
+    b = U.spectrogram2wav_batch(mags, n_iter=10, do_trim=False)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)

@@ -318,7 +318,7 @@ def run_ours(args):
     achieved = my_frames * bytes_per_frame / (fe_kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "traffic": ncu_traffic(args.precision, my_frames),
-                "kernel": "frontend_kernel<%s>" % ("double,7,2,1" if args.precision == "f64" else "float,14,1,2"),
+                "kernel": "frontend_coop_kernel<%s>" % ("double,8,2" if args.precision == "f64" else "float,16,1"),
                 "kernel_ms": fe_kernel_ms, "frames_per_launch": my_frames, "bytes_per_frame": bytes_per_frame,
                 "peak_source": peak_src,
                 "fft_tflops": my_frames * FFT_FLOP / (fe_kernel_ms * 1e-3) / 1e12}

@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_kernel(const GlParams P) 
                     constexpr int j = decltype(jj)::value;
                     const float s = xs[lane + 32 * j];
                     const float pw = fmaf(v[j].x, v[j].x, v[j].y * v[j].y);
-                    const float sc = s * (pw >= 1e-16f ? rsqrtf(pw) : 1e8f);
+                    const float sc = s * rsqrtf(fmaxf(pw, 1e-16f));            // == s / max(1e-8, |est|)
                     v[j] = make_float2(v[j].x * sc, v[j].y * sc);
                 });
                 if (lane == 0) nyq = xs[1024] * (nyq / fmaxf(1e-8f, fabsf(nyq)));

@@ -1,0 +1,309 @@
+// Packed-float32 variant of the warp-level 1024-point complex FFT (fft_warp.cuh): the same 32 x 32 decomposition, with
+// the in-register 32-point transforms issued as f32x2 instructions (FADD2 / FMUL2 / FFMA2 of sm_100).
+//
+// A lane's 32 complex values live as 16 + 16 register pairs, real and imaginary parts apart (Pk).  Two pairings:
+//   layout A: pair j holds elements (j, j + 16)      -- what a radix-2 DIF stage of span 16 leaves independent: after
+//             that first (scalar) stage the two halves are two 16-point transforms with identical structure and
+//             identical twiddles, so stages 2..5 run on pairs with duplicated (c, c) constants;
+//   layout B: pair m holds elements (2 m, 2 m + 1)   -- where the bit-reversed outputs of those stages land
+//             (pair p of layout A ends up holding outputs brev5(p), brev5(p) + 1; renamed at compile time).
+// fft32_ab maps A -> B.  The twiddle between the two passes multiplies pairs of layout B by a table laid out to
+// match, and the transposition writes element n1 of a row to column 2 (n1 % 16) + n1 / 16, so that the 128-bit
+// row reads of the second pass come back as layout-A pairs without a single register move.
+// Per 32-point transform: 175 packed + <= 128 scalar instructions instead of 456 scalar ones.
+//
+// Replaces numpy.fft.rfft / irfft as called by librosa.stft / istft (reference src/utils.py:314, :328).
+#pragma once
+#include "fft_warp.cuh"
+
+namespace unast {
+
+struct Pk { float2 re[16], im[16]; };
+
+// scalar views of element J in the two layouts
+template <int J> __device__ __forceinline__ float& reA(Pk& p) { if constexpr (J < 16) return p.re[J].x; else return p.re[J - 16].y; }
+template <int J> __device__ __forceinline__ float& imA(Pk& p) { if constexpr (J < 16) return p.im[J].x; else return p.im[J - 16].y; }
+template <int J> __device__ __forceinline__ float& reB(Pk& p) { if constexpr (J % 2 == 0) return p.re[J / 2].x; else return p.re[J / 2].y; }
+template <int J> __device__ __forceinline__ float& imB(Pk& p) { if constexpr (J % 2 == 0) return p.im[J / 2].x; else return p.im[J / 2].y; }
+
+__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ float2 dup2(float c) { return make_float2(c, c); }
+
+__host__ __device__ constexpr int brev4(int i) { return ((i & 1) << 3) | ((i & 2) << 1) | ((i & 4) >> 1) | ((i & 8) >> 3); }
+
+// (re, im) * exp(-2 pi i J / 32) on pairs, J in 0..15
+template <int J>
+__device__ __forceinline__ void pk_mul_w32(float2& re, float2& im) {
+    if constexpr (J == 0) {
+    } else if constexpr (J == 8) {
+        const float2 t = re;
+        re = im;
+        im = neg2(t);
+    } else if constexpr (J == 4) {
+        const float2 r = dup2((float)kCos32[4]);
+        const float2 s = __fadd2_rn(re, im), d = __fadd2_rn(im, neg2(re));
+        re = __fmul2_rn(s, r);
+        im = __fmul2_rn(d, r);
+    } else if constexpr (J == 12) {
+        const float2 r = dup2((float)kCos32[4]);
+        const float2 s = __fadd2_rn(re, im), d = __fadd2_rn(im, neg2(re));
+        re = __fmul2_rn(d, r);
+        im = __fmul2_rn(s, neg2(r));
+    } else {
+        const float2 c = dup2((float)cos32(J)), s = dup2((float)sin32(J));   // W = c - i s
+        const float2 nr = __ffma2_rn(re, c, __fmul2_rn(im, s));
+        const float2 ni = __ffma2_rn(im, c, __fmul2_rn(re, neg2(s)));
+        re = nr;
+        im = ni;
+    }
+}
+
+// one DIF stage of the two 16-point halves at once (SPAN = 8, 4, 2, 1 inside a half)
+template <int SPAN>
+__device__ __forceinline__ void pk_stage(Pk& p) {
+    static_for<0, 8>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        constexpr int lo = (i / SPAN) * 2 * SPAN + i % SPAN, hi = lo + SPAN, J = (i % SPAN) * (8 / SPAN) * 2;
+        const float2 ar = p.re[lo], ai = p.im[lo], br = p.re[hi], bi = p.im[hi];
+        p.re[lo] = __fadd2_rn(ar, br);
+        p.im[lo] = __fadd2_rn(ai, bi);
+        float2 dr = __fadd2_rn(ar, neg2(br)), di = __fadd2_rn(ai, neg2(bi));
+        pk_mul_w32<J>(dr, di);
+        p.re[hi] = dr;
+        p.im[hi] = di;
+    });
+}
+
+// In-register 32-point forward FFT, layout A in -> layout B out (natural order).
+// NZ: only elements [0, NZ) are non-zero on entry (16 <= NZ <= 32) -- prunes the scalar first stage.
+template <int NZ>
+__device__ __forceinline__ void fft32_ab(Pk& p) {
+    static_assert(NZ >= 16 && NZ <= 32, "pruning supports 16..32 live inputs");
+    static_for<0, 16>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        const float2 a = make_float2(p.re[j].x, p.im[j].x);
+        if constexpr (j + 16 < NZ) {
+            const float2 b = make_float2(p.re[j].y, p.im[j].y);
+            const float2 t = mul_w32<j>(make_float2(a.x - b.x, a.y - b.y));
+            p.re[j] = make_float2(a.x + b.x, t.x);
+            p.im[j] = make_float2(a.y + b.y, t.y);
+        } else {
+            const float2 t = mul_w32<j>(a);
+            p.re[j].y = t.x;
+            p.im[j].y = t.y;
+        }
+    });
+    pk_stage<8>(p);
+    pk_stage<4>(p);
+    pk_stage<2>(p);
+    pk_stage<1>(p);
+    Pk t;
+    static_for<0, 16>([&](auto mm) { constexpr int m = decltype(mm)::value; t.re[m] = p.re[brev4(m)]; t.im[m] = p.im[brev4(m)]; });
+    p = t;
+}
+
+// column of element n1 in a row of the transposition buffer
+__device__ __forceinline__ int pk_col(int n1) { return 2 * (n1 & 15) + (n1 >> 4); }
+
+// 1024-point complex forward FFT across one warp, split-plane transposition (see warp_fft1024_split).
+// in : layout A, element n2 = z[lane + 32 n2] (only the first NZ elements non-zero)
+// out: layout B, element k2 = Z[lane + 32 k2]
+// tw4: [16][32] float4 (c[2m], c[2m+1], s[2m], s[2m+1]) of W1024^(lane k1) = c + i s, k1 = 2m, 2m + 1
+template <int NZ>
+__device__ __forceinline__ void warp_fft1024_pk(Pk& p, float* xs, const float4* __restrict__ tw4, int lane) {
+    constexpr int XS = XsStride<float>::value;
+    fft32_ab<NZ>(p);
+    static_for<0, 16>([&](auto mm) {
+        constexpr int m = decltype(mm)::value;
+        const float4 w = tw4[m * 32 + lane];
+        const float2 c = make_float2(w.x, w.y), s = make_float2(w.z, w.w);
+        const float2 nr = __ffma2_rn(p.re[m], c, __fmul2_rn(p.im[m], neg2(s)));
+        const float2 ni = __ffma2_rn(p.re[m], s, __fmul2_rn(p.im[m], c));
+        p.re[m] = nr;
+        p.im[m] = ni;
+    });
+    float* col = xs + pk_col(lane);
+    const float4* row = reinterpret_cast<const float4*>(xs + lane * XS);
+    static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; col[k1 * XS] = reB<k1>(p); });
+    __syncwarp();
+    static_for<0, 8>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        const float4 q = row[i];
+        p.re[2 * i] = make_float2(q.x, q.y);
+        p.re[2 * i + 1] = make_float2(q.z, q.w);
+    });
+    __syncwarp();
+    static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; col[k1 * XS] = imB<k1>(p); });
+    __syncwarp();
+    static_for<0, 8>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        const float4 q = row[i];
+        p.im[2 * i] = make_float2(q.x, q.y);
+        p.im[2 * i + 1] = make_float2(q.z, q.w);
+    });
+    __syncwarp();
+    fft32_ab<32>(p);
+}
+
+// (re, im) * (exp(-2 pi i J1 / 32), exp(-2 pi i J2 / 32)): a different twiddle in each half of the pair
+template <int J1, int J2>
+__device__ __forceinline__ void pk_mul_w32_2(float2& re, float2& im) {
+    if constexpr (J1 != 0 || J2 != 0) {
+        const float2 c = make_float2((float)cos32(J1), (float)cos32(J2)), s = make_float2((float)sin32(J1), (float)sin32(J2));
+        const float2 nr = __ffma2_rn(re, c, __fmul2_rn(im, s));
+        const float2 ni = __ffma2_rn(im, c, __fmul2_rn(re, neg2(s)));
+        re = nr;
+        im = ni;
+    }
+}
+
+template <int LO, int HI, int J1, int J2>
+__device__ __forceinline__ void pk_bfly2(Pk& p) {
+    const float2 ar = p.re[LO], ai = p.im[LO], br = p.re[HI], bi = p.im[HI];
+    p.re[LO] = __fadd2_rn(ar, br);
+    p.im[LO] = __fadd2_rn(ai, bi);
+    float2 dr = __fadd2_rn(ar, neg2(br)), di = __fadd2_rn(ai, neg2(bi));
+    pk_mul_w32_2<J1, J2>(dr, di);
+    p.re[HI] = dr;
+    p.im[HI] = di;
+}
+
+// In-register 32-point forward FFT, layout B in -> layout A out (natural order): the radix-2 DIF stages of span
+// 16, 8, 4, 2 act between pairs (element e of a pair and e + 1 take the twiddles W^J and W^(J + 16 / span)), the
+// last stage (span 1) inside each pair.  Pair m ends up holding outputs (brev4(m), brev4(m) + 16).
+__device__ __forceinline__ void fft32_ba(Pk& p) {
+    static_for<0, 8>([&](auto ii) { constexpr int m = decltype(ii)::value; pk_bfly2<m, m + 8, 2 * m, 2 * m + 1>(p); });
+    static_for<0, 8>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        constexpr int mm = i % 4, lo = 8 * (i / 4) + mm;
+        pk_bfly2<lo, lo + 4, 4 * mm, 4 * mm + 2>(p);
+    });
+    static_for<0, 8>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        constexpr int mm = i % 2, lo = 4 * (i / 2) + mm;
+        pk_bfly2<lo, lo + 2, 8 * mm, 8 * mm + 4>(p);
+    });
+    static_for<0, 8>([&](auto ii) { constexpr int i = decltype(ii)::value; pk_bfly2<2 * i, 2 * i + 1, 0, 8>(p); });
+    static_for<0, 16>([&](auto mm) {
+        constexpr int m = decltype(mm)::value;
+        const float2 r = p.re[m], i = p.im[m];
+        p.re[m] = make_float2(r.x + r.y, r.x - r.y);
+        p.im[m] = make_float2(i.x + i.y, i.x - i.y);
+    });
+    Pk t;
+    static_for<0, 16>([&](auto aa) { constexpr int a = decltype(aa)::value; t.re[a] = p.re[brev4(a)]; t.im[a] = p.im[brev4(a)]; });
+    p = t;
+}
+
+// The same transform for an input in layout B (first pass = fft32_ba, twiddle on layout-A pairs).
+// tw4a: [16][32] float4 (c[j], c[j + 16], s[j], s[j + 16]) of W1024^(lane k1), k1 = j, j + 16
+__device__ __forceinline__ void warp_fft1024_pk_b(Pk& p, float* xs, const float4* __restrict__ tw4a, int lane) {
+    constexpr int XS = XsStride<float>::value;
+    fft32_ba(p);
+    static_for<0, 16>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        const float4 w = tw4a[j * 32 + lane];
+        const float2 c = make_float2(w.x, w.y), s = make_float2(w.z, w.w);
+        const float2 nr = __ffma2_rn(p.re[j], c, __fmul2_rn(p.im[j], neg2(s)));
+        const float2 ni = __ffma2_rn(p.re[j], s, __fmul2_rn(p.im[j], c));
+        p.re[j] = nr;
+        p.im[j] = ni;
+    });
+    float* col = xs + pk_col(lane);
+    const float4* row = reinterpret_cast<const float4*>(xs + lane * XS);
+    static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; col[k1 * XS] = reA<k1>(p); });
+    __syncwarp();
+    static_for<0, 8>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        const float4 q = row[i];
+        p.re[2 * i] = make_float2(q.x, q.y);
+        p.re[2 * i + 1] = make_float2(q.z, q.w);
+    });
+    __syncwarp();
+    static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; col[k1 * XS] = imA<k1>(p); });
+    __syncwarp();
+    static_for<0, 8>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        const float4 q = row[i];
+        p.im[2 * i] = make_float2(q.x, q.y);
+        p.im[2 * i + 1] = make_float2(q.z, q.w);
+    });
+    __syncwarp();
+    fft32_ab<32>(p);
+}
+
+// ---- real-FFT post- / pre-processing by mirror pairs, packed ------------------------------------------------
+// Layout B throughout.  Lane l keeps elements 0..15 (pairs m < 8: bins ka = l + 64 m, ka + 32) and fetches their
+// mirrors kb = 1024 - ka, which are elements 31 - 2m, 30 - 2m of lane 32 - l (column 0 pairs with itself: element
+// j <-> 32 - j, and bin 0 with the Nyquist bin), from a park buffer in shared memory: plane[row][slot], 33 rows of
+// PK_PARK_S floats; lane l' parks element e >= 16 at row l', slot 31 - e; lane 0 instead at row 32, slot 32 - e, plus
+// its element 0 at slot 0 -- so that every lane reads its two mirrors with one aligned 64-bit load from one base.
+// After pk_post_pairs: pair m = X[ka] (both halves), pair m + 8 = X[kb] of the same two bins' mirrors.
+// pk_pre_pairs takes that back to Z' (conjugated, times 2, see irfft_pre_shfl): own elements in place, the mirrors
+// returned through the same rows (only lane l and its mirror lane ever touch row 32 - l), then read back as pairs
+// 8..15.  Lane 0's element 16 (bin 512, its own mirror) is handled by the caller through pk_park_512 / row 0 slot 0.
+constexpr int PK_PARK_S = 18;
+constexpr int PK_PARK_PLANE = 33 * PK_PARK_S;             // floats per plane (re, im)
+constexpr int PK_PARK_BYTES = 2 * PK_PARK_PLANE * 4;      // 4752
+
+// wp4: [8][32] float4 (wx[ka0], wx[ka1], wy[ka0], wy[ka1]),  wp2[k] = (wx, wy) = (-sin th, -cos th), th = 2 pi k / 2048
+__device__ __forceinline__ void pk_post_pairs(Pk& p, float* park, const float4* __restrict__ wp4, int lane) {
+    float* pre = park;
+    float* pim = park + PK_PARK_PLANE;
+    {
+        const int wb = lane ? lane * PK_PARK_S : 32 * PK_PARK_S + 1;
+        static_for<8, 16>([&](auto mm) {
+            constexpr int m = decltype(mm)::value;
+            pre[wb + 31 - 2 * m] = p.re[m].x; pre[wb + 30 - 2 * m] = p.re[m].y;
+            pim[wb + 31 - 2 * m] = p.im[m].x; pim[wb + 30 - 2 * m] = p.im[m].y;
+        });
+        if (lane == 0) { pre[32 * PK_PARK_S] = p.re[0].x; pim[32 * PK_PARK_S] = p.im[0].x; }
+    }
+    __syncwarp();
+    const int rb = lane ? (32 - lane) * PK_PARK_S : 32 * PK_PARK_S;
+    static_for<0, 8>([&](auto mm) {
+        constexpr int m = decltype(mm)::value;
+        const float2 qr = *reinterpret_cast<const float2*>(pre + rb + 2 * m), qi = *reinterpret_cast<const float2*>(pim + rb + 2 * m);
+        const float4 w = wp4[m * 32 + lane];
+        const float2 wx = make_float2(w.x, w.y), wy = make_float2(w.z, w.w);
+        const float2 zr = p.re[m], zi = p.im[m];
+        const float2 er = __fadd2_rn(zr, qr), ei = __fadd2_rn(zi, neg2(qi)), orr = __fadd2_rn(zr, neg2(qr)), oi = __fadd2_rn(zi, qi);
+        const float2 A = __ffma2_rn(wx, orr, __fmul2_rn(neg2(wy), oi)), B = __ffma2_rn(wx, oi, __fmul2_rn(wy, orr));
+        p.re[m] = __fadd2_rn(er, A);
+        p.im[m] = __fadd2_rn(B, ei);
+        p.re[m + 8] = __fadd2_rn(er, neg2(A));
+        p.im[m + 8] = __fadd2_rn(B, neg2(ei));
+    });
+}
+
+__device__ __forceinline__ void pk_pre_pairs(Pk& p, float* park, const float4* __restrict__ wp4, int lane) {
+    float* pre = park;
+    float* pim = park + PK_PARK_PLANE;
+    const int wb = lane ? (32 - lane) * PK_PARK_S : 1;
+    static_for<0, 8>([&](auto mm) {
+        constexpr int m = decltype(mm)::value;
+        const float4 w = wp4[m * 32 + lane];
+        const float2 wx = make_float2(w.x, w.y), wy = make_float2(w.z, w.w);
+        const float2 xr = p.re[m], xi = p.im[m], rr = p.re[m + 8], ri = p.im[m + 8];
+        const float2 er = __fadd2_rn(xr, rr), ei = __fadd2_rn(xi, neg2(ri)), dr = __fadd2_rn(xr, neg2(rr)), di = __fadd2_rn(xi, ri);
+        const float2 C = __ffma2_rn(wx, dr, __fmul2_rn(wy, di));
+        const float2 nD = __ffma2_rn(wy, dr, __fmul2_rn(neg2(wx), di));      // -(wx di - wy dr)
+        p.re[m] = __fadd2_rn(er, C);
+        p.im[m] = __fadd2_rn(nD, neg2(ei));                                   // -(D + ei)
+        const float2 br = __fadd2_rn(er, neg2(C)), bi = __fadd2_rn(ei, nD);   // mirror: (er - C, -(D - ei))
+        pre[wb + 15 - 2 * m] = br.x; pre[wb + 14 - 2 * m] = br.y;
+        pim[wb + 15 - 2 * m] = bi.x; pim[wb + 14 - 2 * m] = bi.y;
+    });
+}
+// after the caller has dealt with bin 512 and synchronised the warp: elements 16..31 back from the own row
+__device__ __forceinline__ void pk_pre_collect(Pk& p, const float* park, int lane) {
+    const float* pre = park + lane * PK_PARK_S;
+    const float* pim = pre + PK_PARK_PLANE;
+    static_for<8, 16>([&](auto mm) {
+        constexpr int m = decltype(mm)::value;
+        p.re[m] = *reinterpret_cast<const float2*>(pre + 2 * (m - 8));
+        p.im[m] = *reinterpret_cast<const float2*>(pim + 2 * (m - 8));
+    });
+}
+
+}  // namespace unast

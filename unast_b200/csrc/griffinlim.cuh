@@ -52,6 +52,9 @@ struct GlParams {
     const float2* win2;          // (w[2n], w[2n+1]) / 2
     const float2* wini2;         // (w[2n], w[2n+1]) / 2048 (irfft scaling folded into the synthesis window)
     const float2* tw1024;
+    const float4* tw4;           // packed layout of tw1024 for fft_pk.cuh: [16][32] (c[2m], c[2m+1], s[2m], s[2m+1])
+    const float4* tw4a;          // ... for pairs (j, j + 16): [16][32] (c[j], c[j+16], s[j], s[j+16])
+    const float4* wp4;           // packed wp2: [8][32] (wx[ka], wx[ka+32], wy[ka], wy[ka+32]), ka = lane + 64 m
     const float2* wp2;
     const float2* phi;           // [1025] exp(+2 pi i 473 k / 2048): shift phase applied to the initial spectrum
     const float* rinv_l;         // [GL_EDGE_L] 1 / envelope at padded position q (left edge)

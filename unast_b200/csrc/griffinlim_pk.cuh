@@ -1,0 +1,290 @@
+// K3 (packed): the Griffin-Lim iteration kernel of griffinlim.cuh on the f32x2 FFT core of fft_pk.cuh (replaces
+// reference src/utils.py:309-328 and librosa.griffinlim as called at src/gl_vocoder.py:26).
+//
+// Same state, run partition, carry and seam handling as gl_kernel; what differs, driven by its ncu capture
+// (profiles/r1c_ncu_gl.txt: 4,100 warp instructions per frame and iteration, issue-bound at 64 %):
+//   * the four 32-point transforms, both inter-pass twiddles and the real-FFT post- / pre-processing run on register
+//     pairs (FADD2 / FMUL2 / FFMA2) -- about half the floating-point instructions;
+//   * post- and pre-processing work on mirror pairs (k, 1024 - k) through a small park buffer in shared memory
+//     instead of 256 shuffles with lane-0 selects; everything between the two transforms stays in one layout, in place;
+//   * the frame's target-magnitude row has its own landing zone and is prefetched one frame ahead.
+#pragma once
+#include "griffinlim.cuh"
+#include "fft_pk.cuh"
+
+namespace unast {
+
+constexpr int GLP_XS_BYTES = PK_PARK_BYTES > GL_XS_BYTES ? PK_PARK_BYTES : GL_XS_BYTES;   // 4752: transposition / park buffer
+constexpr int GLP_SROW_BYTES = S_STRIDE * 4;                                               // 4128
+constexpr int GLP_WARP_BYTES = GLP_XS_BYTES + GLP_SROW_BYTES + GL_CARRY * 4;               // 12192
+constexpr int glp_off_warp = 0;
+constexpr int glp_off_wa = glp_off_warp + GL_WARPS * GLP_WARP_BYTES;
+constexpr int glp_off_win = glp_off_wa + (NLIVE_C * 8 + 15) / 16 * 16;
+constexpr int glp_off_wini = glp_off_win + (NLIVE_C * 8 + 15) / 16 * 16;
+constexpr int glp_off_twb = glp_off_wini + (NLIVE_C * 8 + 15) / 16 * 16;
+constexpr int glp_off_twa = glp_off_twb + 512 * 16;
+constexpr int glp_off_wp4 = glp_off_twa + 512 * 16;
+constexpr int glp_smem_bytes = glp_off_wp4 + 256 * 16;
+static_assert(GLP_XS_BYTES % 16 == 0 && GLP_SROW_BYTES % 16 == 0 && glp_smem_bytes <= 227 * 1024, "shared memory layout");
+
+// phase update of one bin (classic: utils.py:315-316; momentum: librosa.griffinlim), S from the row buffer
+template <bool MOMENTUM>
+__device__ __forceinline__ void gl_update_bin(float& xr, float& xi, int k, const float* __restrict__ srow, float2* tp,
+                                              float alpha, bool first_iter) {
+    const float s = srow[k];
+    if (!MOMENTUM) {
+        const float pw = fmaf(xr, xr, xi * xi);
+        const float sc = s * rsqrtf(fmaxf(pw, 1e-16f));                  // == s / max(1e-8, |est|)
+        xr *= sc;
+        xi *= sc;
+    } else {
+        float ar = xr, ai = xi;
+        if (!first_iter) { const float2 pr = tp[k]; ar = fmaf(-alpha, pr.x, ar); ai = fmaf(-alpha, pr.y, ai); }
+        tp[k] = make_float2(xr, xi);
+        const float sc = s / (sqrtf(fmaf(ar, ar, ai * ai)) + 1e-16f);
+        xr = ar * sc;
+        xi = ai * sc;
+    }
+}
+
+template <bool MOMENTUM>
+__global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams P) {
+    constexpr int NT = GL_WARPS * 32;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned char* wbase = smem + glp_off_warp + warp * GLP_WARP_BYTES;
+    float* xs = reinterpret_cast<float*>(wbase);                         // transposition buffer / park buffer / edge scratch
+    float* srow = reinterpret_cast<float*>(wbase + GLP_XS_BYTES);        // landing zone of the frame's target-magnitude row
+    float* cb = reinterpret_cast<float*>(wbase + GLP_XS_BYTES + GLP_SROW_BYTES);
+    float2* s_wa = reinterpret_cast<float2*>(smem + glp_off_wa);
+    float2* s_win = reinterpret_cast<float2*>(smem + glp_off_win);
+    float2* s_wini = reinterpret_cast<float2*>(smem + glp_off_wini);
+    float4* s_twb = reinterpret_cast<float4*>(smem + glp_off_twb);
+    float4* s_twa = reinterpret_cast<float4*>(smem + glp_off_twa);
+    float4* s_wp4 = reinterpret_cast<float4*>(smem + glp_off_wp4);
+
+    for (int i = tid; i < NLIVE_C; i += NT) { s_wa[i] = P.wa2[i]; s_win[i] = P.win2[i]; s_wini[i] = P.wini2[i]; }
+    for (int i = tid; i < 512; i += NT) { s_twb[i] = P.tw4[i]; s_twa[i] = P.tw4a[i]; }
+    for (int i = tid; i < 256; i += NT) s_wp4[i] = P.wp4[i];
+    __syncthreads();                                                    // the only CTA-wide barrier
+
+    // this warp's run of frames: equal shares of the total cost (edge frames are ~1.3x an interior frame)
+    const long long W = (long long)gridDim.x * GL_WARPS, wid = (long long)blockIdx.x * GL_WARPS + warp;
+    const long long total_cost = P.cost_off[P.B];
+    auto frame_at = [&](long long c) -> int {                          // frame that contains cost point c
+        if (c <= 0) return 0;
+        if (c >= total_cost) return P.total_frames;
+        int lo = 0, hi = P.B;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.cost_off[mid] <= c) lo = mid; else hi = mid; }
+        const int T = P.frame_off[lo + 1] - P.frame_off[lo];
+        int ci = (int)(c - P.cost_off[lo]), t;
+        const int head = 5 * min(4, T), inner = 4 * max(0, T - 8);
+        if (ci < head) t = ci / 5;
+        else if (ci < head + inner) t = 4 + (ci - head) / 4;
+        else t = 4 + max(0, T - 8) + (ci - head - inner) / 5;
+        return P.frame_off[lo] + min(t, T - 1);
+    };
+    const int f0 = frame_at((total_cost * wid) / W), f1 = frame_at((total_cost * (wid + 1)) / W);
+    if (f0 >= f1) return;
+    int b;
+    {
+        int lo = 0, hi = P.B;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.frame_off[mid] <= f0) lo = mid; else hi = mid; }
+        b = lo;
+    }
+    bool have_carry = false;        // cb holds the partial sums of this utterance's previous frames
+    long long seam_end = -1;        // positions below this index of ola_w also receive the previous run's tail
+
+    // target-magnitude row of the first frame (every later row is prefetched one frame ahead)
+    for (int c = lane; c < S_STRIDE / 4; c += 32) cp_async16(srow + 4 * c, P.S + (size_t)f0 * S_STRIDE + 4 * c);
+    cp_async_commit();
+
+    for (int f = f0; f < f1; ++f) {
+        if (f >= P.frame_off[b + 1]) { while (f >= P.frame_off[b + 1]) ++b; have_carry = false; }
+        const int fbase = P.frame_off[b];
+        const int Tb = P.frame_off[b + 1] - fbase;
+        const int t = f - fbase;
+        const int L = HOP * (Tb - 1);
+        const long long ubase = P.pad_off[b];
+        const long long pos0 = ubase + HOP * t + WIN_LPAD;             // padded index of the frame's tap 0
+        const bool last_of_utt = t == Tb - 1;
+        const bool last_of_run = f == f1 - 1;
+
+        if (!have_carry) {
+            for (int i = lane; i < GL_CARRY; i += 32) cb[i] = 0.0f;
+            seam_end = -1;
+            if (t > 0) {                                                 // head seam: shared with the previous run's tail
+                seam_end = pos0 + OVERLAP;
+                for (int i = lane; i < OVERLAP; i += 32) P.ola_z[pos0 + i] = 0.0f;
+            }
+            __syncwarp();
+        }
+
+        Pk v;
+        if (P.mode == GL_ITER) {
+            // ---- 1. previous iteration's signal: normalise, reflect-pad, window (layout A) ----
+            if (t >= 4 && t <= Tb - 5) {
+                const float* __restrict__ x = P.ola_r + pos0 + 2 * lane;
+                static_for<0, 18>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    const int n = lane + 32 * j;
+                    if (j < 17 || n < NLIVE_C) {
+                        const float2 w = s_wa[n];
+                        reA<j>(v) = x[64 * j] * w.x;
+                        imA<j>(v) = x[64 * j + 1] * w.y;
+                    } else {
+                        reA<j>(v) = 0.f;
+                        imA<j>(v) = 0.f;
+                    }
+                });
+            } else {
+                // Edge frame (rare): stage the normalised, reflect-padded taps in the idle transposition buffer
+                const float* __restrict__ src = P.ola_r + ubase;
+                const int nbase = HOP * t + WIN_LPAD - HALF;
+                if (Tb >= GL_TABLE_MIN_T) {
+                    const float* __restrict__ rtab = (t < 4) ? P.rinv_l : P.rinv_r + (1100 - WIN_LPAD - HOP * (Tb - 1));
+#pragma unroll 6
+                    for (int i = lane; i < WIN; i += 32) {
+                        int n = abs(nbase + i);                            // reflect at 0
+                        n = min(n, 2 * (L - 1) - n);                       // reflect at L - 1
+                        const int q = n + HALF;
+                        xs[i] = src[q] * rtab[q];
+                    }
+                } else {
+#pragma unroll 1
+                    for (int i = lane; i < WIN; i += 32) {
+                        int n = abs(nbase + i);
+                        n = min(n, 2 * (L - 1) - n);
+                        const int q = n + HALF;
+                        float y = src[q];
+                        const float w = wss_at(q, Tb, P.wss_per, P.w2);
+                        if (w > FLT_MIN) y = y / w;                         // librosa.istft: y[nz] /= wss[nz]
+                        xs[i] = y;
+                    }
+                }
+                __syncwarp();
+                static_for<0, 18>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    const int n = lane + 32 * j;
+                    if (j < 17 || n < NLIVE_C) {
+                        const float2 w = s_win[n];
+                        const float2 y = reinterpret_cast<const float2*>(xs)[n];
+                        reA<j>(v) = y.x * w.x;
+                        imA<j>(v) = y.y * w.y;
+                    } else {
+                        reA<j>(v) = 0.f;
+                        imA<j>(v) = 0.f;
+                    }
+                });
+                __syncwarp();
+            }
+            static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; reA<j>(v) = 0.f; imA<j>(v) = 0.f; });
+            // ---- 2. STFT column (layout B out), mirror pairs: pair m = X[ka], pair m + 8 = X[1024 - ka] ----
+            warp_fft1024_pk<18>(v, xs, s_twb, lane);
+            pk_post_pairs(v, xs, s_wp4, lane);
+        }
+        // ---- 3. phase update against S on the mirror pairs: ka = lane + 64 m (+ 32), kb = 1024 - ka ----
+        cp_async_wait_all();
+        __syncwarp();
+        float2* tp = MOMENTUM ? P.tprev + (size_t)f * NBINS : nullptr;
+        float x512r = 0.f, x512i = 0.f;                                  // lane 0: bin 512, its own mirror
+        if (P.mode == GL_ITER) {
+            static_for<0, 8>([&](auto mm) {
+                constexpr int m = decltype(mm)::value;
+                const int ka = lane + 64 * m;
+                gl_update_bin<MOMENTUM>(v.re[m].x, v.im[m].x, ka, srow, tp, P.alpha, P.first_iter);
+                gl_update_bin<MOMENTUM>(v.re[m].y, v.im[m].y, ka + 32, srow, tp, P.alpha, P.first_iter);
+                gl_update_bin<MOMENTUM>(v.re[m + 8].x, v.im[m + 8].x, 1024 - ka, srow, tp, P.alpha, P.first_iter);
+                gl_update_bin<MOMENTUM>(v.re[m + 8].y, v.im[m + 8].y, 992 - ka, srow, tp, P.alpha, P.first_iter);
+            });
+            if (lane == 0) {
+                x512r = 2.0f * xs[32 * PK_PARK_S + 16];                  // X[512] = 2 conj(z), z parked by pk_post_pairs
+                x512i = -2.0f * xs[PK_PARK_PLANE + 32 * PK_PARK_S + 16];
+                gl_update_bin<MOMENTUM>(x512r, x512i, 512, srow, tp, P.alpha, P.first_iter);
+            }
+        } else {
+            // initial spectrum S * angles0 in the shifted frame
+            const float2* a0 = P.angles0 ? P.angles0 + (size_t)f * NBINS : nullptr;
+            auto init_bin = [&](float& xr, float& xi, int k) {
+                float2 ph = P.phi[k];
+                if (a0) ph = cmul(a0[k], ph);
+                const float s = srow[k];
+                xr = s * ph.x;
+                xi = s * ph.y;
+            };
+            static_for<0, 8>([&](auto mm) {
+                constexpr int m = decltype(mm)::value;
+                const int ka = lane + 64 * m;
+                init_bin(v.re[m].x, v.im[m].x, ka);
+                init_bin(v.re[m].y, v.im[m].y, ka + 32);
+                init_bin(v.re[m + 8].x, v.im[m + 8].x, 1024 - ka);
+                init_bin(v.re[m + 8].y, v.im[m + 8].y, 992 - ka);
+            });
+            if (lane == 0) {
+                v.im[0].x = 0.0f;                                        // irfft ignores Im of the DC bin
+                v.im[8].x = 0.0f;                                        // ... and of the Nyquist bin
+                init_bin(x512r, x512i, 512);
+            }
+        }
+        // ---- 4. back to Z' (layout B, in place; mirrors through the park buffer), ISTFT column ----
+        pk_pre_pairs(v, xs, s_wp4, lane);
+        if (lane == 0) { xs[0] = 2.0f * x512r; xs[PK_PARK_PLANE] = 2.0f * x512i; }   // element 16 of lane 0
+        __syncwarp();
+        if (f + 1 < f1) {                                               // next frame's S row (this one has been consumed)
+            const float* Snext = P.S + (size_t)(f + 1) * S_STRIDE;
+            for (int c = lane; c < S_STRIDE / 4; c += 32) cp_async16(srow + 4 * c, Snext + 4 * c);
+        }
+        cp_async_commit();
+        pk_pre_collect(v, xs, lane);
+        __syncwarp();
+        warp_fft1024_pk_b(v, xs, s_twa, lane);
+
+        // ---- 5. window, overlap-add with the carried partial sums, emit what became final ----
+        // tap i of this frame sits at ola_w[pos0 + i]; taps [0, 275) are complete once this frame is added
+        // (given the carry), taps [275, 1102) become the next frame's carry [0, 827).
+        static_for<0, 18>([&](auto jj) {
+            constexpr int j = decltype(jj)::value;
+            const int n = lane + 32 * j;
+            if (j < 17 || n < NLIVE_C) {
+                const float2 w = s_wini[n];
+                const int i0 = 2 * n;
+                float o0 = reB<j>(v) * w.x, o1 = -imB<j>(v) * w.y;
+                if (j < 12 || i0 < OVERLAP) {                            // carry covers taps [0, 827); cb[827] == 0
+                    const float2 c = *reinterpret_cast<const float2*>(cb + i0);
+                    o0 += c.x;
+                    o1 += c.y;
+                }
+                auto put = [&](int i, float val) {
+                    if (i < HOP) {
+                        const long long q = pos0 + i;
+                        if (q < seam_end) atomicAdd(P.ola_w + q, val);
+                        else P.ola_w[q] = val;
+                    } else {
+                        cb[i - HOP] = val;
+                    }
+                };
+                if (j < 4) { put(i0, o0); put(i0 + 1, o1); }             // i0 + 1 <= 255 < 275: always emitted
+                else if (j == 4) { put(i0, o0); put(i0 + 1, o1); }       // straddles tap 275
+                else { cb[i0 - HOP] = o0; cb[i0 + 1 - HOP] = o1; }
+            }
+        });
+        __syncwarp();
+        have_carry = true;
+        if (last_of_utt || last_of_run) {
+            // flush the carry: final at the end of an utterance, otherwise the tail seam shared with the next run
+            const long long q0 = pos0 + HOP;
+            if (last_of_utt) {
+                for (int i = lane; i < OVERLAP; i += 32) {
+                    const long long q = q0 + i;
+                    if (q < seam_end) atomicAdd(P.ola_w + q, cb[i]); else P.ola_w[q] = cb[i];
+                }
+            } else {
+                for (int i = lane; i < OVERLAP; i += 32) atomicAdd(P.ola_w + q0 + i, cb[i]);
+            }
+            __syncwarp();
+            have_carry = false;
+        }
+    }
+}
+
+}  // namespace unast

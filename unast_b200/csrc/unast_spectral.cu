@@ -10,10 +10,24 @@
 
 #include "../../include/unast_spectral.h"
 #include "frontend.cuh"
+#include "frontend_pf.cuh"
 #include "griffinlim.cuh"
+#include "griffinlim_pk.cuh"
 #include "trim.cuh"
 
 using namespace unast;
+
+// Griffin-Lim iteration kernel: 1 = packed f32x2 FFT core (griffinlim_pk.cuh), 0 = scalar (griffinlim.cuh)
+#ifndef UNAST_GL_PK
+#define UNAST_GL_PK 1
+#endif
+#if UNAST_GL_PK
+#define GL_KERNEL gl_pk_kernel
+#define GL_SMEM glp_smem_bytes
+#else
+#define GL_KERNEL gl_kernel
+#define GL_SMEM gl_smem_bytes
+#endif
 
 // Front-end kernel configurations.  Default: the cooperative kernel (every warp an FFT warp, mel phase shared by all
 // warps); -DUNAST_FE_SPECIALISED=1 selects the warp-specialised variant (dedicated mel warps) for A/B runs.
@@ -35,11 +49,24 @@ constexpr int FE_F32_THREADS = (14 + 2) * 32;
 constexpr int FE_F64_THREADS = (UNAST_FE64_FW + 1) * 32;
 #else
 using FeF32 = FeCoopLayout<float, 16, 1>;
-using FeF64 = FeCoopLayout<double, 8, 2>;
 #define FE_F32_KERNEL frontend_coop_kernel<float, 16, 1>
-#define FE_F64_KERNEL frontend_coop_kernel<double, 8, 2>
 constexpr int FE_F32_THREADS = 16 * 32;
+// float64: UNAST_FE64_PF = number of warps of the prefetching split-exchange kernel (frontend_pf.cuh); 0 = the
+// two-frames-per-warp cooperative kernel
+#ifndef UNAST_FE64_PF
+#define UNAST_FE64_PF 12
+#endif
+#if UNAST_FE64_PF
+using FeF64 = FePfLayout<double, UNAST_FE64_PF>;
+#define FE_F64_KERNEL frontend_pf_kernel<double, UNAST_FE64_PF>
+constexpr int FE_F64_THREADS = UNAST_FE64_PF * 32;
+#define FE_F64_COOP coopN
+#else
+using FeF64 = FeCoopLayout<double, 8, 2>;
+#define FE_F64_KERNEL frontend_coop_kernel<double, 8, 2>
 constexpr int FE_F64_THREADS = 8 * 32;
+#define FE_F64_COOP coop8
+#endif
 #endif
 
 namespace {
@@ -105,6 +132,8 @@ struct unast_ctx {
     int num_sms = 0;
     // analysis windows carry the 1/2 of the real-FFT post-processing (and 2^-15 for PCM16 input)
     float2 *win2_f = nullptr, *win2i_f = nullptr, *wini2_f = nullptr, *tw_f = nullptr, *wp_f = nullptr, *phi_f = nullptr;
+    float4 *tw4a_f = nullptr, *wp4_f = nullptr;
+    float4* tw4_f = nullptr;                                    // tw_f in the packed layout of fft_pk.cuh
     double2 *win2_d = nullptr, *win2i_d = nullptr, *tw_d = nullptr, *wp_d = nullptr;
     float *wss_per = nullptr, *rinv_l = nullptr, *rinv_r = nullptr;
     float2* wa2_f = nullptr;
@@ -112,8 +141,8 @@ struct unast_ctx {
     float2* bfrag = nullptr;
     int* pair_kb = nullptr;
     int pair_begin[11] = {0};
-    MelUnit* units8 = nullptr; MelUnit* units16 = nullptr;   // cooperative mel phase: unit lists for 8 / 16 warps
-    MelCoop coop8, coop16;
+    MelUnit* units8 = nullptr; MelUnit* units16 = nullptr; MelUnit* unitsN = nullptr;   // cooperative mel phase: unit lists for 8 / 16 warps
+    MelCoop coop8, coop16, coopN;
     int* d_err = nullptr;
     std::vector<float> mel_basis;
 };
@@ -260,11 +289,28 @@ int unast_create(int device, unast_ctx** out) {
             tw_d[k1 * 32 + n1] = make_double2(std::cos(th), -std::sin(th));
             tw_f[k1 * 32 + n1] = make_float2((float)std::cos(th), (float)-std::sin(th));
         }
+    std::vector<float4> tw4_f(512);
+    for (int m = 0; m < 16; ++m)
+        for (int n1 = 0; n1 < 32; ++n1) {
+            const float2 a = tw_f[(2 * m) * 32 + n1], b = tw_f[(2 * m + 1) * 32 + n1];
+            tw4_f[m * 32 + n1] = make_float4(a.x, b.x, a.y, b.y);
+        }
     for (int k = 0; k < 1024; ++k) {
         const double th = 2.0 * kPi * k / 2048.0;
         wp_d[k] = make_double2(-std::sin(th), -std::cos(th));
         wp_f[k] = make_float2((float)(-std::sin(th)), (float)(-std::cos(th)));
     }
+    std::vector<float4> tw4a_f(512), wp4_f(256);
+    for (int j = 0; j < 16; ++j)
+        for (int n1 = 0; n1 < 32; ++n1) {
+            const float2 a = tw_f[j * 32 + n1], b = tw_f[(j + 16) * 32 + n1];
+            tw4a_f[j * 32 + n1] = make_float4(a.x, b.x, a.y, b.y);
+        }
+    for (int m = 0; m < 8; ++m)
+        for (int l = 0; l < 32; ++l) {
+            const float2 a = wp_f[l + 64 * m], b = wp_f[l + 64 * m + 32];
+            wp4_f[m * 32 + l] = make_float4(a.x, b.x, a.y, b.y);
+        }
     for (int k = 0; k < NBINS; ++k) {
         const double th = 2.0 * kPi * ((WIN_LPAD * k) % NFFT) / NFFT;
         phi_f[k] = make_float2((float)std::cos(th), (float)std::sin(th));
@@ -324,7 +370,7 @@ int unast_create(int device, unast_ctx** out) {
     c->pair_begin[NMELS / 8] = (int)pair_kb.size();
     // Cooperative mel phase: n-tiles (split in two halves when clearly above the per-warp share) dealt to the warps
     // longest-first; a warp's units are stored contiguously in the order it visits them.
-    std::vector<MelUnit> h_units8, h_units16;
+    std::vector<MelUnit> h_units8, h_units16, h_unitsN;
     auto build_coop = [&](int FW, std::vector<MelUnit>& out, MelCoop& mc) {
         const int total = c->pair_begin[NMELS / 8];
         const double share = (double)total / FW;
@@ -361,24 +407,25 @@ int unast_create(int device, unast_ctx** out) {
     };
     build_coop(8, h_units8, c->coop8);
     build_coop(16, h_units16, c->coop16);
+    build_coop(UNAST_FE64_PF ? UNAST_FE64_PF : 8, h_unitsN, c->coopN);
 
     cudaError_t e = cudaSuccess;
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
     up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
     up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
-    up(&c->units8, h_units8); up(&c->units16, h_units16);
+    up(&c->tw4_f, tw4_f); up(&c->tw4a_f, tw4a_f); up(&c->wp4_f, wp4_f); up(&c->units8, h_units8); up(&c->units16, h_units16); up(&c->unitsN, h_unitsN);
     up(&c->wa2_f, wa2_f); up(&c->rinv_l, rinv_l); up(&c->rinv_r, rinv_r);
     up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F32_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF32::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F64_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF64::bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, gl_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(GL_KERNEL<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GL_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(GL_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GL_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
-    c->coop8.units = c->units8; c->coop16.units = c->units16;
-    if ((int)h_units8.size() > MEL_MAX_UNITS || (int)h_units16.size() > MEL_MAX_UNITS) { unast_destroy(c); return fail(UNAST_E_ARG, "unast_create: mel unit table too large"); }
+    c->coop8.units = c->units8; c->coop16.units = c->units16; c->coopN.units = c->unitsN;
+    if ((int)h_units8.size() > MEL_MAX_UNITS || (int)h_units16.size() > MEL_MAX_UNITS || (int)h_unitsN.size() > MEL_MAX_UNITS) { unast_destroy(c); return fail(UNAST_E_ARG, "unast_create: mel unit table too large"); }
     *out = c;
     return UNAST_OK;
 }
@@ -387,7 +434,7 @@ int unast_destroy(unast_ctx* c) {
     if (!c) return UNAST_OK;
     cudaFree(c->win2_f); cudaFree(c->win2i_f); cudaFree(c->win2i_d); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
     cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
-    cudaFree(c->units8); cudaFree(c->units16);
+    cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f); cudaFree(c->units8); cudaFree(c->units16); cudaFree(c->unitsN);
     cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
     cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
     delete c;
@@ -481,7 +528,7 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
 #if UNAST_FE_SPECIALISED
         FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P);
 #else
-        FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P, c->coop8);
+        FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P, c->FE_F64_COOP);
 #endif
     }
     CU(cudaGetLastError());
@@ -556,13 +603,13 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
     P.angles0 = (const float2*)angles0;
     P.alpha = momentum / (1.0f + momentum);
-    P.wa2 = c->wa2_f; P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw1024 = c->tw_f; P.wp2 = c->wp_f; P.phi = c->phi_f;
+    P.wa2 = c->wa2_f; P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw1024 = c->tw_f; P.tw4 = c->tw4_f; P.tw4a = c->tw4a_f; P.wp4 = c->wp4_f; P.wp2 = c->wp_f; P.phi = c->phi_f;
     P.rinv_l = c->rinv_l; P.rinv_r = c->rinv_r; P.wss_per = c->wss_per; P.w2 = c->w2;
     // one run of frames per warp; keep runs >= 8 frames so that seams (atomics) stay a small share
     const int grid = (int)std::max<long long>(1, std::min<long long>(c->num_sms, p.total_frames / (8 * GL_WARPS)));
     auto launch = [&]() {
-        if (momentum != 0.f) gl_kernel<true><<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
-        else gl_kernel<false><<<grid, GL_WARPS * 32, gl_smem_bytes, st>>>(P);
+        if (momentum != 0.f) GL_KERNEL<true><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);
+        else GL_KERNEL<false><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);
     };
     P.mode = GL_INIT; P.first_iter = 1; P.ola_r = nullptr; P.ola_w = ola[1]; P.ola_z = ola[2];
     launch();

@@ -197,7 +197,8 @@ __device__ __forceinline__ void fft32_ba(Pk& p) {
 
 // The same transform for an input in layout B (first pass = fft32_ba, twiddle on layout-A pairs).
 // tw4a: [16][32] float4 (c[j], c[j + 16], s[j], s[j + 16]) of W1024^(lane k1), k1 = j, j + 16
-__device__ __forceinline__ void warp_fft1024_pk_b(Pk& p, float* xs, const float4* __restrict__ tw4a, int lane) {
+template <class F>
+__device__ __forceinline__ void warp_fft1024_pk_b(Pk& p, float* xs, const float4* __restrict__ tw4a, int lane, F&& xs_idle) {
     constexpr int XS = XsStride<float>::value;
     fft32_ba(p);
     static_for<0, 16>([&](auto jj) {
@@ -229,6 +230,7 @@ __device__ __forceinline__ void warp_fft1024_pk_b(Pk& p, float* xs, const float4
         p.im[2 * i + 1] = make_float2(q.z, q.w);
     });
     __syncwarp();
+    xs_idle();                                   // the buffer is free from here on (e.g. to prefetch into)
     fft32_ab<32>(p);
 }
 

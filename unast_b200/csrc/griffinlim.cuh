@@ -39,6 +39,7 @@ struct GlParams {
     const long long* pad_off;    // [B+1] prefix sum of Lp_b = 2048 + 275 (T_b - 1)
     int B;
     int total_frames;
+    const int4* runs;            // [gridDim.x * GL_WARPS] (first frame, end frame, utterance of the first frame) per warp
     const long long* cost_off;   // [B+1] prefix sum of the utterances' cost (interior frame 4, edge frame 5): run partition
     const float* ola_r;          // read buffer  (unused in GL_INIT)
     float* ola_w;                // write buffer

@@ -68,30 +68,12 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
     for (int i = tid; i < 256; i += NT) s_wp4[i] = P.wp4[i];
     __syncthreads();                                                    // the only CTA-wide barrier
 
-    // this warp's run of frames: equal shares of the total cost (edge frames are ~1.3x an interior frame)
-    const long long W = (long long)gridDim.x * GL_WARPS, wid = (long long)blockIdx.x * GL_WARPS + warp;
-    const long long total_cost = P.cost_off[P.B];
-    auto frame_at = [&](long long c) -> int {                          // frame that contains cost point c
-        if (c <= 0) return 0;
-        if (c >= total_cost) return P.total_frames;
-        int lo = 0, hi = P.B;
-        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.cost_off[mid] <= c) lo = mid; else hi = mid; }
-        const int T = P.frame_off[lo + 1] - P.frame_off[lo];
-        int ci = (int)(c - P.cost_off[lo]), t;
-        const int head = 5 * min(4, T), inner = 4 * max(0, T - 8);
-        if (ci < head) t = ci / 5;
-        else if (ci < head + inner) t = 4 + (ci - head) / 4;
-        else t = 4 + max(0, T - 8) + (ci - head - inner) / 5;
-        return P.frame_off[lo] + min(t, T - 1);
-    };
-    const int f0 = frame_at((total_cost * wid) / W), f1 = frame_at((total_cost * (wid + 1)) / W);
+    // this warp's run of frames (equal shares of a cost that weights edge frames; resolved once on the host)
+    const int4 run = P.runs[blockIdx.x * GL_WARPS + warp];
+    const int f0 = run.x, f1 = run.y;
     if (f0 >= f1) return;
-    int b;
-    {
-        int lo = 0, hi = P.B;
-        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (P.frame_off[mid] <= f0) lo = mid; else hi = mid; }
-        b = lo;
-    }
+    int b = run.z;
+    bool x_staged = false;          // this frame's input samples were prefetched into xs by the previous frame
     bool have_carry = false;        // cb holds the partial sums of this utterance's previous frames
     long long seam_end = -1;        // positions below this index of ola_w also receive the previous run's tail
 
@@ -123,7 +105,25 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
         Pk v;
         if (P.mode == GL_ITER) {
             // ---- 1. previous iteration's signal: normalise, reflect-pad, window (layout A) ----
-            if (t >= 4 && t <= Tb - 5) {
+            if (x_staged) {
+                // interior frame whose taps the previous frame prefetched (16-byte chunks from pos0 & ~3)
+                cp_async_wait_all();
+                __syncwarp();
+                const float* x = xs + (int)(pos0 & 3) + 2 * lane;
+                static_for<0, 18>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    const int n = lane + 32 * j;
+                    if (j < 17 || n < NLIVE_C) {
+                        const float2 w = s_wa[n];
+                        reA<j>(v) = x[64 * j] * w.x;
+                        imA<j>(v) = x[64 * j + 1] * w.y;
+                    } else {
+                        reA<j>(v) = 0.f;
+                        imA<j>(v) = 0.f;
+                    }
+                });
+                __syncwarp();
+            } else if (t >= 4 && t <= Tb - 5) {
                 const float* __restrict__ x = P.ola_r + pos0 + 2 * lane;
                 static_for<0, 18>([&](auto jj) {
                     constexpr int j = decltype(jj)::value;
@@ -237,7 +237,15 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
         cp_async_commit();
         pk_pre_collect(v, xs, lane);
         __syncwarp();
-        warp_fft1024_pk_b(v, xs, s_twa, lane);
+        // the next frame's taps go into the transposition buffer as soon as the inverse transform is done with it
+        x_staged = P.mode == GL_ITER && f + 1 < f1 && t + 1 >= 4 && t + 1 <= Tb - 5;
+        warp_fft1024_pk_b(v, xs, s_twa, lane, [&]() {
+            if (x_staged) {
+                const float* src = P.ola_r + ((pos0 + HOP) & ~3LL);
+                for (int c = lane; c < (WIN + 3 + 3) / 4; c += 32) cp_async16(xs + 4 * c, src + 4 * c);
+                cp_async_commit();
+            }
+        });
 
         // ---- 5. window, overlap-add with the carried partial sums, emit what became final ----
         // tap i of this frame sits at ola_w[pos0 + i]; taps [0, 275) are complete once this frame is added

@@ -537,12 +537,13 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
 
 // ---- Griffin-Lim ----
 namespace {
+constexpr int GL_MAX_RUNS = 8192;                                  // >= SMs x GL_WARPS: one run of frames per warp
 struct GlPlan {
     std::vector<int> frame_off;
     std::vector<long long> pad_off, wav_off, cost_off;
     long long total_frames = 0, total_pad = 0, total_wav = 0;
     int max_wav = 0;
-    size_t o_meta_i = 0, o_meta_l = 0, o_S = 0, o_ola = 0, o_tprev = 0, o_be = 0, bytes = 0;
+    size_t o_runs = 0, o_meta_i = 0, o_meta_l = 0, o_S = 0, o_ola = 0, o_tprev = 0, o_be = 0, bytes = 0;
 };
 bool gl_plan(const int32_t* frames, int B, float momentum, GlPlan& p) {
     p.frame_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.wav_off.assign(B + 1, 0); p.cost_off.assign(B + 1, 0);
@@ -557,6 +558,7 @@ bool gl_plan(const int32_t* frames, int B, float momentum, GlPlan& p) {
     }
     p.total_frames = p.frame_off[B]; p.total_pad = p.pad_off[B]; p.total_wav = p.wav_off[B];
     size_t o = 0;
+    p.o_runs = o; o += align256((size_t)GL_MAX_RUNS * sizeof(int4));
     p.o_meta_i = o; o += align256(2 * (size_t)(B + 1) * sizeof(int));
     p.o_meta_l = o; o += align256(3 * (size_t)(B + 1) * sizeof(long long));
     p.o_S = o; o += align256((size_t)p.total_frames * S_STRIDE * sizeof(float));
@@ -607,6 +609,34 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     P.rinv_l = c->rinv_l; P.rinv_r = c->rinv_r; P.wss_per = c->wss_per; P.w2 = c->w2;
     // one run of frames per warp; keep runs >= 8 frames so that seams (atomics) stay a small share
     const int grid = (int)std::max<long long>(1, std::min<long long>(c->num_sms, p.total_frames / (8 * GL_WARPS)));
+    // The run partition is the same for every iteration: resolve it once on the host (equal shares of the cost that
+    // weights edge frames 5 : 4; see GlPlan::cost_off) instead of by dependent global loads at every launch.
+    {
+        const long long W = (long long)grid * GL_WARPS, total_cost = p.cost_off[B];
+        if (W > GL_MAX_RUNS) return fail(UNAST_E_ARG, "unast_griffinlim: too many SMs for the run table");
+        auto frame_at = [&](long long cpt) -> int {
+            if (cpt <= 0) return 0;
+            if (cpt >= total_cost) return (int)p.total_frames;
+            int lo = 0, hi = B;
+            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (p.cost_off[mid] <= cpt) lo = mid; else hi = mid; }
+            const int T = p.frame_off[lo + 1] - p.frame_off[lo];
+            const int ci = (int)(cpt - p.cost_off[lo]), head = 5 * std::min(4, T), inner = 4 * std::max(0, T - 8);
+            int t;
+            if (ci < head) t = ci / 5;
+            else if (ci < head + inner) t = 4 + (ci - head) / 4;
+            else t = 4 + std::max(0, T - 8) + (ci - head - inner) / 5;
+            return p.frame_off[lo] + std::min(t, T - 1);
+        };
+        std::vector<int4> runs((size_t)W);
+        int b = 0;
+        for (long long w = 0; w < W; ++w) {
+            const int f0 = frame_at(total_cost * w / W), f1 = frame_at(total_cost * (w + 1) / W);
+            while (b + 1 < B && p.frame_off[b + 1] <= f0) ++b;
+            runs[(size_t)w] = make_int4(f0, f1, b, 0);
+        }
+        CU(cudaMemcpyAsync(ws + p.o_runs, runs.data(), (size_t)W * sizeof(int4), cudaMemcpyHostToDevice, st));
+        P.runs = (const int4*)(ws + p.o_runs);
+    }
     auto launch = [&]() {
         if (momentum != 0.f) GL_KERNEL<true><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);
         else GL_KERNEL<false><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);

@@ -233,6 +233,16 @@ def ncu_traffic(precision, frames):
         return None
 
 
+def gl_traffic(frames):
+    """DRAM bytes of one Griffin-Lim iteration launch from the committed ncu capture, scaled per frame; None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as fh:
+            rec = json.load(fh)["gl_iteration"]
+        return rec["dram_bytes"] / rec["frames"] * frames
+    except Exception:
+        return None
+
+
 def run_ours(args):
     import torch
     from unast_b200 import dist as D
@@ -318,7 +328,7 @@ def run_ours(args):
     achieved = my_frames * bytes_per_frame / (fe_kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "traffic": ncu_traffic(args.precision, my_frames),
-                "kernel": "frontend_coop_kernel<%s>" % ("double,8,2" if args.precision == "f64" else "float,16,1"),
+                "kernel": "frontend_pf_kernel<double,12>" if args.precision == "f64" else "frontend_coop_kernel<float,16,1>",
                 "kernel_ms": fe_kernel_ms, "frames_per_launch": my_frames, "bytes_per_frame": bytes_per_frame,
                 "peak_source": peak_src,
                 "fft_tflops": my_frames * FFT_FLOP / (fe_kernel_ms * 1e-3) / 1e12}
@@ -483,6 +493,7 @@ def run_gl(args, eng, clocks, pool, rank, world, D):
             "value": total_audio / (ms * 1e-3), "unit": "audio-s/s", "ms_per_step": ms, "steps": gl_steps, "scaling": "weak",
             "frames_per_rank": n_frames, "gpu_launches_per_step": int(launches), "dtype": "f32",
             "roofline": {"bound": "fp32", "achieved": flop / (ms * 1e-3) / 1e12, "peak": None, "unit": "TFLOP/s", "frac": None,
+                         "kernel": "gl_pk_kernel<false>", "traffic": gl_traffic(n_frames),
                          "flop_per_frame": (2 * args.gl_iters + 1) * FFT_FLOP,
                          "note": "whole step (all %d launches); algorithmic flop = (2 n_iter + 1) x 2.5 N log2 N per frame" % launches},
             "e2e": {"value": total_audio / (e2e_ms * 1e-3), "unit": "audio-s/s", "ms_per_step": e2e_ms,

@@ -96,6 +96,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     } while (!done);
 }
 
+// the same wait as one opaque statement (the retry loop lives inside the PTX block): no loop in the compiler's control
+// flow graph, so a wait in the middle of a register-heavy section does not perturb register allocation
+__device__ __forceinline__ void mbar_wait_inline(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "LAB_WAIT:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONE;\n\t"
+        "bra LAB_WAIT;\n\t"
+        "DONE:\n\t}"
+        ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+
 // ---- tensor memory (TMEM) as a per-SM operand store ----------------------------------------------------
 // 512 columns x 128 lanes x 32 bit per SM.  A warp reaches the 32 lanes of its own quadrant (warp id % 4) with the
 // 32x32b shape: thread i <-> lane 32 (warp % 4) + i, consecutive registers <-> consecutive columns.
@@ -139,6 +153,12 @@ __device__ __forceinline__ void tmem_wait_ld(float4& v) {
 __device__ __forceinline__ void tmem_wait_ld(float4& v, float4& w) {
     asm volatile("tcgen05.wait::ld.sync.aligned;"
                  : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w), "+f"(w.x), "+f"(w.y), "+f"(w.z), "+f"(w.w)::"memory");
+}
+
+__device__ __forceinline__ void tmem_wait_ld(float4& a, float4& b, float4& c, float4& d) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+f"(a.x), "+f"(a.y), "+f"(a.z), "+f"(a.w), "+f"(b.x), "+f"(b.y), "+f"(b.z), "+f"(b.w),
+                   "+f"(c.x), "+f"(c.y), "+f"(c.z), "+f"(c.w), "+f"(d.x), "+f"(d.y), "+f"(d.z), "+f"(d.w)::"memory");
 }
 
 // ---- cp.async (LDGSTS) helpers: 16-byte global -> shared copies that bypass registers ------------------

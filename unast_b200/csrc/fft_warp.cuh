@@ -237,8 +237,10 @@ template <> struct XsStride<float> { static constexpr int value = 36; };    // 1
 template <> struct XsStride<double> { static constexpr int value = 34; };   // 272 B rows
 template <class T> __host__ __device__ constexpr int xs_bytes() { return 32 * XsStride<T>::value * (int)sizeof(T); }
 
-template <class T, int NZ>
-__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const cplx_t<T>* __restrict__ tw, int lane) {
+// mid(): called between the two planes, where only the 32 imaginary parts are live in registers -- the cheapest point
+// of the transform for anything that needs registers of its own (e.g. a barrier wait).
+template <class T, int NZ, class MID>
+__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const cplx_t<T>* __restrict__ tw, int lane, MID&& mid) {
     using C = cplx_t<T>;
     constexpr int XS = XsStride<T>::value;
     fft32<NZ>(v);
@@ -262,6 +264,7 @@ __device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, co
     };
     static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; xs[k1 * XS + lane] = v[k1].x; });
     __syncwarp();
+    mid();
     read_row([](C& c) -> T& { return c.x; });
     __syncwarp();
     static_for<0, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; xs[k1 * XS + lane] = v[k1].y; });
@@ -269,6 +272,11 @@ __device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, co
     read_row([](C& c) -> T& { return c.y; });
     __syncwarp();
     fft32<32>(v);
+}
+
+template <class T, int NZ>
+__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const cplx_t<T>* __restrict__ tw, int lane) {
+    warp_fft1024_split<T, NZ>(v, xs, tw, lane, []() {});
 }
 
 __device__ __forceinline__ float2 shfl_c(float2 a, int src) {

@@ -41,14 +41,17 @@ struct FePfLayout {
     static constexpr int off_part = off_units + MEL_MAX_UNITS * 16;
     static constexpr int off_ti = off_part + 4 * 128 * 4;                // TileInfo ring [4] + the current utterance record
     static constexpr int off_tmem = off_ti + 5 * 32;
-    static constexpr int bytes = off_tmem + 16;
+    static constexpr int off_bar = off_tmem + 16;
+    static constexpr int off_cnt = off_bar + 16;                        // arrival counters of the split n-tiles
+    static constexpr int off_loop = off_cnt + 16;                       // per-warp tile counters (see the tile loop)
+    static constexpr int bytes = off_loop + 16 * 4;
     static_assert(R <= 16, "a tile is one m16 MMA tile of frames");
     static_assert(bytes <= 227 * 1024, "shared memory budget");
 };
 
 // Real-FFT post-processing by pairs.  in: v[j] = Z[lane + 32 j] / 2.  Lane l computes, for j < 16, bin ka = l + 32 j
-// and its mirror kb = 1024 - ka (lane 0, j = 0: DC and Nyquist) and hands both to emit(ka, Xa, kb, Xb); lane 0 also
-// emits bin 512.  With w = wp2[ka] = (-sin th, -cos th):
+// and its mirror kb = 1024 - ka (lane 0, j = 0: DC and Nyquist) and hands both to emit(j, Xa, Xb); lane 0 also
+// emits bin 512 through emit512(X).  With w = wp2[ka] = (-sin th, -cos th):
 //   er = z.x + p.x, ei = z.y - p.y, or = z.x - p.x, oi = z.y + p.y   (p = Z[1024 - ka] / 2)
 //   A = w.x or - w.y oi, B = w.x oi + w.y or;   X[ka] = (er + A, B + ei),  X[kb] = (er - A, B - ei).
 // The mirror value of (lane l, register j) sits in lane 32 - l, register 31 - j (column 0 pairs with itself:
@@ -56,8 +59,8 @@ struct FePfLayout {
 // 32 - j' (rows 1..16, 32 complex values each), lane 0 also its register 0 in row 0; then lane l >= 1 reads row
 // j + 1, column 32 - l and lane 0 reads row j, column 0 -- one base pointer per lane, no selects, and only the 16
 // lower registers stay live in the pair loop (room to batch the loads).  buf: 17 x 32 complex values.
-template <class T, class WP, class F>
-__device__ __forceinline__ void rfft_post_pairs(cplx_t<T> (&v)[32], cplx_t<T>* buf, const WP& wp, int lane, F&& emit) {
+template <class T, class WP, class F, class G>
+__device__ __forceinline__ void rfft_post_pairs(cplx_t<T> (&v)[32], cplx_t<T>* buf, const WP& wp, int lane, F&& emit, G&& emit512) {
     using C = cplx_t<T>;
     static_for<16, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; buf[(32 - j) * 32 + lane] = v[j]; });
     if (lane == 0) buf[0] = v[0];
@@ -69,11 +72,11 @@ __device__ __forceinline__ void rfft_post_pairs(cplx_t<T> (&v)[32], cplx_t<T>* b
         const C z = v[j], w = wp.template get<j>(lane);
         const T er = z.x + p.x, ei = z.y - p.y, orr = z.x - p.x, oi = z.y + p.y;
         const T A = fma_t(w.x, orr, -(w.y * oi)), B = fma_t(w.x, oi, w.y * orr);
-        emit(lane + 32 * j, mk(er + A, B + ei), 1024 - lane - 32 * j, mk(er - A, B - ei));
+        emit(jj, mk(er + A, B + ei), mk(er - A, B - ei));
     });
     if (lane == 0) {                                  // bin 512 (register 16 of lane 0) pairs with itself: X = 2 conj(z)
         const C z = buf[16 * 32];
-        emit(512, mk(z.x + z.x, -(z.y + z.y)), -1, mk((T)0, (T)0));
+        emit512(mk(z.x + z.x, -(z.y + z.y)));
     }
     __syncwarp();
 }
@@ -183,6 +186,9 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_pf_kernel(const FrontendP
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::off_tmem);
     TileInfo* s_ti = reinterpret_cast<TileInfo*>(smem + L::off_ti);      // ring [4], slot g & 3
     UttRec* s_utt = reinterpret_cast<UttRec*>(smem + L::off_ti + 4 * 32);
+    uint64_t* bar_empty = reinterpret_cast<uint64_t*>(smem + L::off_bar);
+    int* s_cnt = reinterpret_cast<int*>(smem + L::off_cnt);
+    volatile int* s_it = reinterpret_cast<volatile int*>(smem + L::off_loop) + warp;
 
     const int total_tiles = P.tile_off[P.B];
     const int g0 = (int)(((long long)total_tiles * blockIdx.x) / gridDim.x);
@@ -201,6 +207,11 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_pf_kernel(const FrontendP
     for (int i = tid; i < 4 * 128; i += NT) part[i] = 0.0f;
     for (int i = tid; i < L::NR * ROW_STRIDE; i += NT) rows[i] = 0.0f;
     if (warp == 0) tmem_alloc(s_tmem, 512);                               // whole tensor memory: one CTA per SM
+    if (tid < 4) s_cnt[tid] = 0;
+    if (tid == 0) {
+        mbar_init(bar_empty, FW);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     if (tid == NT - 1) {
         // binary search: last b with tile_off[b] <= g0; then the first two tiles of the ring
         int lo = 0, hi = P.B;
@@ -214,13 +225,17 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_pf_kernel(const FrontendP
     tmem_fence_before_sync();
     __syncthreads();
     tmem_fence_after_sync();
-    const uint32_t tbase = *s_tmem + ((uint32_t)(32 * (warp & 3)) << 16) + 128u * (uint32_t)(warp >> 2);   // <= 64 pairs per warp
+    const uint32_t tbase = *s_tmem + ((uint32_t)(32 * (warp & 3)) << 16) + 128u * (uint32_t)(warp >> 2);   // <= 31 pairs per warp
     const int u0 = M.unit_begin[warp], u1 = M.unit_begin[warp + 1];
-    {   // this warp's B fragments -> tensor memory, in visiting order
+    {   // this warp's B fragments -> tensor memory, in visiting order, already split for 3xTF32: 4 columns per pair
         int lp = 0;
         for (int u = u0; u < u1; ++u)
-            for (int p = s_units[u].p0; p < s_units[u].p1; ++p, ++lp)
-                tmem_st2(tbase + 2 * lp, __ldg(P.mel.bfrag + p * 32 + lane));
+            for (int p = s_units[u].p0; p < s_units[u].p1; ++p, ++lp) {
+                const float2 bw = __ldg(P.mel.bfrag + p * 32 + lane);
+                const uint32_t h0 = tf32_hi(bw.x), h1 = tf32_hi(bw.y);
+                tmem_st4(tbase + 4 * lp, make_float4(__uint_as_float(h0), __uint_as_float(h1),
+                                                     bw.x - __uint_as_float(h0), bw.y - __uint_as_float(h1)));
+            }
         tmem_wait_st();
     }
 
@@ -243,7 +258,14 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_pf_kernel(const FrontendP
         if (prefetched(ti)) pf_issue(P.wave, ti.wbase, ti.ta + f, stage, lane);
     }
 
-    for (int g = g0; g < g1; ++g) {
+    // The loop state is CTA-uniform but, next to 128 registers of frame data, the register allocator spills it to
+    // local memory and every reload stalls on the long scoreboard.  Keeping the warp's tile counter in shared memory
+    // and re-reading it where it is needed (volatile) keeps it out of the long live ranges.
+    if (lane == 0) *s_it = 0;
+    __syncwarp();
+    const int n_tiles = g1 - g0;
+    for (int it = 0; it < n_tiles; it = *s_it) {
+        const int g = g0 + it;
         if (tid == NT - 1 && g + 2 < g1) {                                // resolve tile g + 2 (read after two barriers)
             UttRec u = *s_utt;
             s_ti[(g + 2) & 3] = tile_of(P, u, g + 2, R);
@@ -273,27 +295,49 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_pf_kernel(const FrontendP
                 const TileInfo nxt = s_ti[(g + 1) & 3];
                 if (prefetched(nxt)) pf_issue(P.wave, nxt.wbase, nxt.ta + f, stage, lane);
             }
+            float* row = rows + f * ROW_STRIDE;
+            float* mrow = P.mag_out ? P.mag_out + (size_t)(cur.fbase + t) * NBINS : nullptr;
+            // Rows are about to be overwritten: every warp must have finished its mel share of the previous tile.  It
+            // arrived on an mbarrier long ago, so this wait is normally free (unlike a second CTA barrier); it sits in
+            // the middle of the transform, where the fewest registers are live.
+            auto rows_free = [&]() { const int i2 = *s_it; if (i2 > 0) mbar_wait_inline(bar_empty, (uint32_t)(i2 - 1) & 1u); };
+            if (live) warp_fft1024_split<T, 18>(v, xs, s_tw, lane, rows_free);
+            else rows_free();
             if (live) {
-                float* row = rows + f * ROW_STRIDE;
-                float* mrow = P.mag_out ? P.mag_out + (size_t)(cur.fbase + t) * NBINS : nullptr;
-                warp_fft1024_split<T, 18>(v, xs, s_tw, lane);
-                rfft_post_pairs<T>(v, reinterpret_cast<C*>(xs), wp, lane, [&](int ka, C xa, int kb, C xb) {
+                // power of every bin first (the float64 registers die pair by pair), then the float32 epilogue with 33
+                // independent chains in flight
+                float pa[16], pb[16], p512 = 0.0f;
+                rfft_post_pairs<T>(v, reinterpret_cast<C*>(xs), wp, lane, [&](auto jj, C xa, C xb) {
+                    constexpr int j = decltype(jj)::value;
                     const float ar = (float)xa.x, ai = (float)xa.y;      // complex64 storage of librosa.stft
-                    const float pa = fmaf(ar, ar, ai * ai);
-                    row[ka] = sqrt_approx(pa);                            // np.abs
-                    if (mrow) mrow[ka] = db_norm_pw_nf(pa);
-                    if (kb >= 0) {
-                        const float br = (float)xb.x, bi = (float)xb.y;
-                        const float pb = fmaf(br, br, bi * bi);
-                        row[kb] = sqrt_approx(pb);
-                        if (mrow) mrow[kb] = db_norm_pw_nf(pb);
-                    }
+                    const float br = (float)xb.x, bi = (float)xb.y;
+                    pa[j] = fmaf(ar, ar, ai * ai);
+                    pb[j] = fmaf(br, br, bi * bi);
+                }, [&](C x) { const float r = (float)x.x, i = (float)x.y; p512 = fmaf(r, r, i * i); });
+                float* rowa = row + lane;
+                float* rowb = row + 1024 - lane;
+                static_for<0, 16>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    rowa[32 * j] = sqrt_approx(pa[j]);                    // np.abs
+                    rowb[-32 * j] = sqrt_approx(pb[j]);
                 });
+                if (lane == 0) row[512] = sqrt_approx(p512);
+                if (mrow) {
+                    float* ma = mrow + lane;
+                    float* mb = mrow + 1024 - lane;
+                    static_for<0, 16>([&](auto jj) {
+                        constexpr int j = decltype(jj)::value;
+                        ma[32 * j] = db_norm_pw_nf(pa[j]);
+                        mb[-32 * j] = db_norm_pw_nf(pb[j]);
+                    });
+                    if (lane == 0) mrow[512] = db_norm_pw_nf(p512);
+                }
             }
         }
         __syncthreads();                                                  // rows of the tile complete
         // ---------------- phase 2: this warp's mel units (3xTF32 mma.sync, banded) ----------------
-        const TileInfo cur = s_ti[g & 3];
+        const int it2 = *s_it;
+        const TileInfo cur = s_ti[(g0 + it2) & 3];
         int lp = 0;
         for (int u = u0; u < u1; ++u) {
             const MelUnit un = s_units[u];
@@ -302,49 +346,62 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_pf_kernel(const FrontendP
             for (int a = 0; a < 4; ++a)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[a][q] = 0.f;
-            auto pair_ops = [&](int kb, float b0, float b1, float (&d)[4]) {
+            // B operands (hi0, hi1, lo0, lo1 per pair) come from tensor memory a chunk of four pairs ahead of their use
+            auto pair_ops = [&](int kb, const float4 bq, float (&d)[4]) {
                 float a[4] = {a_lo[8 * kb], a_hi[8 * kb], a_lo[8 * kb + 4], a_hi[8 * kb + 4]};
                 uint32_t ah[4], al[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) { ah[q] = tf32_hi(a[q]); al[q] = tf32_lo(a[q], ah[q]); }
-                const uint32_t b0h = tf32_hi(b0), b1h = tf32_hi(b1);
-                mma_tf32(d, al, b0h, b1h);
-                mma_tf32(d, ah, tf32_lo(b0, b0h), tf32_lo(b1, b1h));
-                mma_tf32(d, ah, b0h, b1h);
+                mma_tf32(d, al, __float_as_uint(bq.x), __float_as_uint(bq.y));
+                mma_tf32(d, ah, __float_as_uint(bq.z), __float_as_uint(bq.w));
+                mma_tf32(d, ah, __float_as_uint(bq.x), __float_as_uint(bq.y));
             };
-            int p = un.p0;
-            for (; p + 4 <= un.p1; p += 4, lp += 4) {
-                float4 q0 = tmem_ld4(tbase + 2 * lp), q1 = tmem_ld4(tbase + 2 * lp + 4);
-                tmem_wait_ld(q0, q1);
-                pair_ops(s_kb[p], q0.x, q0.y, acc[0]);
-                pair_ops(s_kb[p + 1], q0.z, q0.w, acc[1]);
-                pair_ops(s_kb[p + 2], q1.x, q1.y, acc[2]);
-                pair_ops(s_kb[p + 3], q1.z, q1.w, acc[3]);
+            auto load4 = [&](float4 (&q)[4], int l) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) q[i] = tmem_ld4(tbase + 4 * (l + i));
+            };
+            float4 nb[4];
+            load4(nb, lp);
+            for (int p = un.p0; p < un.p1; p += 4, lp += 4) {
+                tmem_wait_ld(nb[0], nb[1], nb[2], nb[3]);
+                const float4 b0 = nb[0], b1 = nb[1], b2 = nb[2], b3 = nb[3];
+                if (p + 4 < un.p1) load4(nb, lp + 4);
+                pair_ops(s_kb[p], b0, acc[0]);
+                if (p + 1 < un.p1) pair_ops(s_kb[p + 1], b1, acc[1]);
+                if (p + 2 < un.p1) pair_ops(s_kb[p + 2], b2, acc[2]);
+                if (p + 3 < un.p1) pair_ops(s_kb[p + 3], b3, acc[3]);
             }
-            for (; p < un.p1; ++p, ++lp) {
-                float2 bw = tmem_ld2(tbase + 2 * lp), dummy = bw;
-                tmem_wait_ld(bw, dummy);
-                pair_ops(s_kb[p], bw.x, bw.y, acc[0]);
-            }
+            lp -= (4 - ((un.p1 - un.p0) & 3)) & 3;                        // the last chunk may have been partial
             float s4[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) s4[q] = (acc[0][q] + acc[1][q]) + (acc[2][q] + acc[3][q]);
             if (un.split >= 0) {
+                // half of an n-tile: add into the shared tile (two contributions onto zero: order-independent); the
+                // warp that arrives second turns the sum into mel and clears the tile for the next one
                 float* dst = part + un.split * 128 + lane * 4;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) atomicAdd(dst + q, s4[q]);
+                __threadfence_block();
+                __syncwarp();
+                int old = 0;
+                if (lane == 0) old = atomicAdd(s_cnt + un.split, 1);
+                old = __shfl_sync(0xffffffffu, old, 0);
+                if (old == 1) {
+                    __threadfence_block();
+                    float t4[4] = {dst[0], dst[1], dst[2], dst[3]};
+                    dst[0] = dst[1] = dst[2] = dst[3] = 0.0f;
+                    if (lane == 0) s_cnt[un.split] = 0;
+                    store_mel_tile(P, cur, un.nt, t4, gq, tq);
+                }
             } else {
                 store_mel_tile(P, cur, un.nt, s4, gq, tq);
             }
         }
-        __syncthreads();                                                  // rows free again, split tiles complete
-        if (warp < M.nsplit) {
-            float* src = part + warp * 128 + lane * 4;
-            float s4[4] = {src[0], src[1], src[2], src[3]};
-            src[0] = src[1] = src[2] = src[3] = 0.0f;
-            store_mel_tile(P, cur, M.split_nt[warp], s4, gq, tq);
-        }
+        __syncwarp();
+        if (lane == 0) { mbar_arrive(bar_empty); *s_it = it2 + 1; }       // this warp is done with the tile's rows
+        __syncwarp();
     }
+    __syncthreads();
     __syncthreads();
     if (warp == 0) tmem_dealloc(*s_tmem, 512);
 }

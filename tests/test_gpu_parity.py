@@ -111,6 +111,19 @@ def test_frontend_int16_equals_float_input():
     assert np.array_equal(mel_i, mel_f) and np.array_equal(mag_i, mag_f)
 
 
+def test_frontend_int16_prefetch_alignments():
+    """PCM16 batch whose utterances start at every alignment inside a 16-byte chunk (the cp.async sample prefetch of the
+    float64 kernel copies aligned chunks and picks the samples out by offset): bit-identical to the float input path."""
+    from unast_b200 import synth, utils as U
+    rng = np.random.RandomState(11)
+    lens = [275 * 14 + 3 + k for k in range(9)] + [275 * 30 + 1, 275 * 40 + 6]
+    qs = [synth.to_pcm16(0.3 * rng.randn(n).astype(np.float32)) for n in lens]
+    res_i = U.spectrograms_from_waves(qs, do_trim=False)
+    res_f = U.spectrograms_from_waves([q.astype(np.float32) / np.float32(32768.0) for q in qs], do_trim=False)
+    for (mel_i, mag_i), (mel_f, mag_f) in zip(res_i, res_f):
+        assert np.array_equal(mel_i, mel_f) and np.array_equal(mag_i, mag_f)
+
+
 def test_frontend_without_trim_and_minimum_length():
     from unast_b200 import utils as U
     rng = np.random.RandomState(5)
@@ -324,11 +337,11 @@ def test_vocode_cli_files(tmp_path):
 # structure-specific edge cases of the kernels (tile / run boundaries, short utterances)
 # ------------------------------------------------------------------------------------------------
 def test_frontend_tile_boundaries_ragged_frame_counts():
-    """Frame counts around multiples of the 16-frame tile (15, 16, 17, 31, 32, 33 frames) and a batch large enough
-    that several CTAs share an utterance: every frame must land in the right row."""
+    """Frame counts around multiples of the 12-frame (float64 kernel) and 16-frame (float32 kernel) tiles and a batch
+    large enough that several CTAs share an utterance: every frame must land in the right row."""
     from unast_b200 import utils as U
     rng = np.random.RandomState(7)
-    lens = [275 * (t - 1) + int(rng.randint(0, 275)) for t in (15, 16, 17, 31, 32, 33, 5, 48)]
+    lens = [275 * (t - 1) + int(rng.randint(0, 275)) for t in (11, 12, 13, 15, 16, 17, 23, 24, 25, 31, 32, 33, 5, 48)]
     waves = [0.2 * rng.randn(n).astype(np.float32) for n in lens]
     res = U.spectrograms_from_waves(waves, do_trim=False)
     for w, (mel, mag) in zip(waves, res):

@@ -11,6 +11,7 @@
 #include "../../include/unast_spectral.h"
 #include "frontend.cuh"
 #include "frontend_pf.cuh"
+#include "frontend_ws.cuh"
 #include "griffinlim.cuh"
 #include "griffinlim_pk.cuh"
 #include "trim.cuh"
@@ -56,7 +57,16 @@ constexpr int FE_F32_THREADS = 16 * 32;
 #ifndef UNAST_FE64_PF
 #define UNAST_FE64_PF 12
 #endif
-#if UNAST_FE64_PF
+// UNAST_FE64_WS = 1: the warp-specialised kernel (frontend_ws.cuh: 12 FFT warps + 4 mel warps)
+#ifndef UNAST_FE64_WS
+#define UNAST_FE64_WS 0
+#endif
+#if UNAST_FE64_WS
+using FeF64 = FeWsLayout<double>;
+#define FE_F64_KERNEL frontend_ws_kernel<double>
+constexpr int FE_F64_THREADS = (WS_FW + WS_MW) * 32;
+#define FE_F64_COOP coop4
+#elif UNAST_FE64_PF
 using FeF64 = FePfLayout<double, UNAST_FE64_PF>;
 #define FE_F64_KERNEL frontend_pf_kernel<double, UNAST_FE64_PF>
 constexpr int FE_F64_THREADS = UNAST_FE64_PF * 32;
@@ -141,8 +151,8 @@ struct unast_ctx {
     float2* bfrag = nullptr;
     int* pair_kb = nullptr;
     int pair_begin[11] = {0};
-    MelUnit* units8 = nullptr; MelUnit* units16 = nullptr; MelUnit* unitsN = nullptr;   // cooperative mel phase: unit lists for 8 / 16 warps
-    MelCoop coop8, coop16, coopN;
+    MelUnit* units8 = nullptr; MelUnit* units16 = nullptr; MelUnit* unitsN = nullptr; MelUnit* units4 = nullptr;   // cooperative mel phase: unit lists for 8 / 16 warps
+    MelCoop coop8, coop16, coopN, coop4;
     int* d_err = nullptr;
     std::vector<float> mel_basis;
 };
@@ -370,7 +380,7 @@ int unast_create(int device, unast_ctx** out) {
     c->pair_begin[NMELS / 8] = (int)pair_kb.size();
     // Cooperative mel phase: n-tiles (split in two halves when clearly above the per-warp share) dealt to the warps
     // longest-first; a warp's units are stored contiguously in the order it visits them.
-    std::vector<MelUnit> h_units8, h_units16, h_unitsN;
+    std::vector<MelUnit> h_units8, h_units16, h_unitsN, h_units4;
     auto build_coop = [&](int FW, std::vector<MelUnit>& out, MelCoop& mc) {
         const int total = c->pair_begin[NMELS / 8];
         const double share = (double)total / FW;
@@ -408,12 +418,13 @@ int unast_create(int device, unast_ctx** out) {
     build_coop(8, h_units8, c->coop8);
     build_coop(16, h_units16, c->coop16);
     build_coop(UNAST_FE64_PF ? UNAST_FE64_PF : 8, h_unitsN, c->coopN);
+    build_coop(4, h_units4, c->coop4);
 
     cudaError_t e = cudaSuccess;
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
     up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
     up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
-    up(&c->tw4_f, tw4_f); up(&c->tw4a_f, tw4a_f); up(&c->wp4_f, wp4_f); up(&c->units8, h_units8); up(&c->units16, h_units16); up(&c->unitsN, h_unitsN);
+    up(&c->tw4_f, tw4_f); up(&c->tw4a_f, tw4a_f); up(&c->wp4_f, wp4_f); up(&c->units8, h_units8); up(&c->units16, h_units16); up(&c->unitsN, h_unitsN); up(&c->units4, h_units4);
     up(&c->wa2_f, wa2_f); up(&c->rinv_l, rinv_l); up(&c->rinv_r, rinv_r);
     up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
@@ -424,7 +435,7 @@ int unast_create(int device, unast_ctx** out) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(GL_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GL_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
-    c->coop8.units = c->units8; c->coop16.units = c->units16; c->coopN.units = c->unitsN;
+    c->coop8.units = c->units8; c->coop16.units = c->units16; c->coopN.units = c->unitsN; c->coop4.units = c->units4;
     if ((int)h_units8.size() > MEL_MAX_UNITS || (int)h_units16.size() > MEL_MAX_UNITS || (int)h_unitsN.size() > MEL_MAX_UNITS) { unast_destroy(c); return fail(UNAST_E_ARG, "unast_create: mel unit table too large"); }
     *out = c;
     return UNAST_OK;
@@ -434,7 +445,7 @@ int unast_destroy(unast_ctx* c) {
     if (!c) return UNAST_OK;
     cudaFree(c->win2_f); cudaFree(c->win2i_f); cudaFree(c->win2i_d); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
     cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
-    cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f); cudaFree(c->units8); cudaFree(c->units16); cudaFree(c->unitsN);
+    cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f); cudaFree(c->units8); cudaFree(c->units16); cudaFree(c->unitsN); cudaFree(c->units4);
     cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
     cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
     delete c;

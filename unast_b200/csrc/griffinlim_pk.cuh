@@ -63,10 +63,15 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
     float4* s_twa = reinterpret_cast<float4*>(smem + glp_off_twa);
     float4* s_wp4 = reinterpret_cast<float4*>(smem + glp_off_wp4);
 
+    // Programmatic dependent launch: the next iteration's grid may start as soon as SMs free up -- its CTAs load the
+    // constant tables while the tail of this grid is still running -- and waits below for this grid to complete
+    // before it touches anything an iteration writes.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     for (int i = tid; i < NLIVE_C; i += NT) { s_wa[i] = P.wa2[i]; s_win[i] = P.win2[i]; s_wini[i] = P.wini2[i]; }
     for (int i = tid; i < 512; i += NT) { s_twb[i] = P.tw4[i]; s_twa[i] = P.tw4a[i]; }
     for (int i = tid; i < 256; i += NT) s_wp4[i] = P.wp4[i];
     __syncthreads();                                                    // the only CTA-wide barrier
+    if (P.mode != GL_ITER) asm volatile("griddepcontrol.wait;" ::: "memory");   // S itself comes from the previous kernel
 
     // this warp's run of frames (equal shares of a cost that weights edge frames; resolved once on the host)
     const int4 run = P.runs[blockIdx.x * GL_WARPS + warp];
@@ -80,6 +85,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
     // target-magnitude row of the first frame (every later row is prefetched one frame ahead)
     for (int c = lane; c < S_STRIDE / 4; c += 32) cp_async16(srow + 4 * c, P.S + (size_t)f0 * S_STRIDE + 4 * c);
     cp_async_commit();
+    if (P.mode == GL_ITER) asm volatile("griddepcontrol.wait;" ::: "memory");   // the previous iteration is complete
 
     for (int f = f0; f < f1; ++f) {
         if (f >= P.frame_off[b + 1]) { while (f >= P.frame_off[b + 1]) ++b; have_carry = false; }

@@ -649,8 +649,20 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
         P.runs = (const int4*)(ws + p.o_runs);
     }
     auto launch = [&]() {
+#if UNAST_GL_PK
+        // programmatic dependent launch (see the kernel's prologue)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GL_WARPS * 32); cfg.dynamicSmemBytes = GL_SMEM; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        if (momentum != 0.f) cudaLaunchKernelEx(&cfg, GL_KERNEL<true>, P);
+        else cudaLaunchKernelEx(&cfg, GL_KERNEL<false>, P);
+#else
         if (momentum != 0.f) GL_KERNEL<true><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);
         else GL_KERNEL<false><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);
+#endif
     };
     P.mode = GL_INIT; P.first_iter = 1; P.ola_r = nullptr; P.ola_w = ola[1]; P.ola_z = ola[2];
     launch();

@@ -329,3 +329,49 @@ def spectral_convergence(y, S):
     E = np.abs(stft(np.asarray(y, dtype=np.float32)))
     T = min(E.shape[1], S.shape[1])
     return float(np.linalg.norm(E[:, :T] - S[:, :T]) / np.linalg.norm(S[:, :T]))
+
+
+# ---- loader side: src/preprocess.py:82-121, :149-155, :176-182 restated in numpy -------------
+def _pad_mel(inputs):
+    """src/preprocess.py:176-182"""
+    max_len = max((x.shape[0] for x in inputs))
+    return np.stack([np.pad(x, [[0, max_len - x.shape[0]], [0, 0]], mode="constant", constant_values=0) for x in inputs])
+
+
+def _prepare_data(inputs):
+    """src/preprocess.py:149-155"""
+    max_len = max((len(x) for x in inputs))
+    return np.stack([np.pad(x, (0, max_len - x.shape[0]), mode="constant", constant_values=0) for x in inputs])
+
+
+def collate_fn_transformer(batch):
+    """src/preprocess.py:82-121 line by line on items {'text', 'mel', 'text_length', 'mel_length'[, 'fname']};
+    returns numpy arrays (text int64, mel float32, text_length int64, mel_length int64)[, fnames]."""
+    text = [d["text"] for d in batch]
+    mel = [d["mel"] for d in batch]
+    mel_length = [d["mel_length"] for d in batch]
+    text_length = [d["text_length"] for d in batch]
+    fnames = None
+    if "fname" in batch[0]:
+        fnames = [d["fname"] for d in batch]
+        fnames = [i for i, _ in sorted(zip(fnames, text_length), key=lambda x: x[1], reverse=True)]
+    text = [i for i, _ in sorted(zip(text, text_length), key=lambda x: x[1], reverse=True)]
+    mel = [i for i, _ in sorted(zip(mel, text_length), key=lambda x: x[1], reverse=True)]
+    mel_length = [i for i, _ in sorted(zip(mel_length, text_length), key=lambda x: x[1], reverse=True)]
+    text_length = sorted(text_length, reverse=True)
+    text = _prepare_data(text).astype(np.int32)
+    mel = _pad_mel(mel)
+    out = (text.astype(np.int64), mel.astype(np.float32), np.asarray(text_length, np.int64), np.asarray(mel_length, np.int64))
+    return (out, fnames) if fnames is not None else out
+
+
+def loader_items_from_waves(texts, waves, fnames=None):
+    """LJDatasets.__getitem__ (src/preprocess.py:34-51) with the mel that prepare_data.py would have written for `wave`."""
+    items = []
+    for i, (tx, w) in enumerate(zip(texts, waves)):
+        mel, _ = spectrograms_from_wave(w)
+        d = {"text": np.asarray(tx, np.int32), "mel": mel, "text_length": len(tx), "mel_length": mel.shape[0]}
+        if fnames is not None:
+            d["fname"] = fnames[i]
+        items.append(d)
+    return items

@@ -372,3 +372,31 @@ def test_griffin_lim_is_deterministic():
     b = U.spectrogram2wav_batch(mags, n_iter=10, do_trim=False)
     for x, y in zip(a, b):
         assert np.array_equal(x, y)
+
+
+def test_loader_collate_on_the_fly_matches_reference_collate():
+    """collate_fn_transformer (src/preprocess.py:82-121) with mels computed on the fly: order (text length descending,
+    ties stable), zero padding, dtypes and values against the oracle's line-by-line restatement."""
+    torch = _torch()
+    from unast_b200 import preprocess as PP
+    rng = np.random.RandomState(21)
+    waves = _clips([(1.3, 60), (2.2, 61), (1.0, 62), (1.8, 63), (1.5, 64)])
+    tlen = [7, 12, 7, 3, 12]                                              # ties: stable order inside equal lengths
+    texts = [rng.randint(1, 70, size=n).astype(np.int32) for n in tlen]
+    names = ["a", "b", "c", "d", "e"]
+    ref, ref_names = so.collate_fn_transformer(so.loader_items_from_waves(texts, waves, names))
+    batch = [{"text": tx, "wave": w, "text_length": len(tx), "fname": n} for tx, w, n in zip(texts, waves, names)]
+    (text, mel, text_length, mel_length), got_names = PP.collate_fn_transformer(batch)
+    assert got_names == ref_names == ["b", "e", "a", "c", "d"]
+    assert text.dtype == torch.long and mel.dtype == torch.float32 and mel.is_cuda
+    assert np.array_equal(text.cpu().numpy(), ref[0]) and np.array_equal(text_length.cpu().numpy(), ref[2])
+    assert np.array_equal(mel_length.cpu().numpy(), ref[3])
+    assert tuple(mel.shape) == ref[1].shape
+    m = mel.cpu().numpy()
+    assert np.abs(m - ref[1]).max() <= TOL
+    for b, T in enumerate(ref[3]):
+        assert np.all(m[b, T:] == 0)
+    # mel-only branch of collate_fn_postnet: batch order kept
+    mel2, lens2, names2 = PP.collate_fn_postnet_mel(batch)
+    assert names2 == names and lens2 == [so.spectrograms_from_wave(w)[0].shape[0] for w in waves]
+    assert np.abs(mel2.cpu().numpy()[0, :lens2[0]] - so.spectrograms_from_wave(waves[0])[0]).max() <= TOL

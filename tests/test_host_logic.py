@@ -174,3 +174,17 @@ def test_world_size_2_sharding_over_gloo(tmp_path):
     owners = r["owners"]
     assert sorted(owners[0] + owners[1]) == list(range(400)) and not set(owners[0]) & set(owners[1])
     assert r["slowest"] / (r["total"] / 2) < 1.01                                   # balanced to < 1 %
+
+
+def test_loader_sort_is_the_reference_permutation():
+    """unast_b200.preprocess sorts like src/preprocess.py:98-104: descending text length, ties in original order."""
+    from unast_b200 import preprocess as PP
+    from oracle import spectral_oracle as so
+    rng = np.random.RandomState(3)
+    tlen = [5, 9, 5, 2, 9, 9, 1]
+    batch = [{"text": rng.randint(1, 50, size=n).astype(np.int32), "text_length": n, "fname": str(i)} for i, n in enumerate(tlen)]
+    order, tl = PP._sort_by_text_length(batch)
+    ref = [i for i, _ in sorted(zip(range(len(tlen)), tlen), key=lambda x: x[1], reverse=True)]
+    assert order == ref == [1, 4, 5, 0, 2, 3, 6] and tl == tlen
+    padded = PP._prepare_data([batch[i]["text"] for i in order])
+    assert np.array_equal(padded, so._prepare_data([batch[i]["text"] for i in order])) and padded.shape == (7, 9)

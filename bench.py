@@ -378,6 +378,7 @@ def run_ours(args):
     # ---- secondary workload C3: 100-iteration Griffin-Lim on 64 spectrograms per rank -----------
     gl = run_gl(args, eng, clocks, pool, rank, world, D)
     loader = run_loader(args, eng, pool, rank) if rank == 0 else None
+    longform = run_longform(args, eng, pool, rank, world, D)
 
     # ---- pipe peaks (roofline denominators MEASURED_PEAKS.json lacks) ---------------------------
     pipes = {k: eng.pipe_peak_tflops(k) for k in ("f32", "f32x2", "f64")}
@@ -414,12 +415,68 @@ def run_ours(args):
                            (my_frames * bytes_per_frame) / 1e9),
                        "fft_precision": args.precision, "pool_clips": args.pool},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "gl": gl, "loader": loader, "pipe_peaks_tflops": pipes, "parity_spot_check": spot,
+            "cpu_baseline": cpu_baseline, "gl": gl, "loader": loader, "longform": longform, "pipe_peaks_tflops": pipes, "parity_spot_check": spot,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
+
+
+def run_longform(args, eng, pool, rank, world, D):
+    """C5 (BASELINE.json configs[4]): one long waveform; the front end's frames are sharded over the ranks with a halo
+    (unast_b200.longform, no exchange); the 100-iteration Griffin-Lim round trip of the whole clip runs on rank 0 only
+    (replicas: sharding it would need a seam exchange per iteration).  Latency regime -- reported, not headlined."""
+    import torch
+    from unast_b200 import longform as LF
+    secs = args.longform_seconds
+    if secs <= 0:
+        return None
+    n = int(secs * SR)
+    reps = -(-n // pool[0].size)
+    w = np.concatenate([pool[(3 * i) % len(pool)] for i in range(reps)])[:n].astype(np.int16)
+    T = 1 + n // HOP
+    a, b = LF.frame_ranges(T, world)[rank]
+    c0, c1, keep = LF.chunk_for_range(n, a, b)
+    dev = eng.device
+    chunk = torch.from_numpy(w[c0:c1].copy()).to(dev)
+    nc = c1 - c0
+    off = torch.tensor([0, nc], dtype=torch.int64, device=dev)
+    bounds = torch.tensor([[0, nc]], dtype=torch.int32, device=dev)
+    fo = eng.frame_offsets(bounds)
+    Tc = int(fo.cpu().numpy()[-1])
+    mel = torch.empty(NMELS * Tc, dtype=torch.float32, device=dev)
+    mag = torch.empty((Tc, NBINS), dtype=torch.float32, device=dev)
+    for _ in range(3):
+        eng.frontend(chunk, off, bounds, fo, Tc, precision=args.precision, mel_out=mel, mag_out=mag)
+    D.barrier()
+    torch.cuda.synchronize()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(10):
+        eng.frontend(chunk, off, bounds, fo, Tc, precision=args.precision, mel_out=mel, mag_out=mag)
+    t1.record()
+    torch.cuda.synchronize()
+    D.barrier()
+    fe_ms = D.max_over_ranks(t0.elapsed_time(t1) / 10)
+    out = {"workload": "C5 (BASELINE.json configs[4]): %d s waveform, %d frames; front end sharded by frame range over %d rank(s) "
+                       "with a %d-frame halo, no exchange" % (secs, T, world, LF.HALO),
+           "frontend": {"value": secs / (fe_ms * 1e-3), "unit": "audio-s/s", "ms": fe_ms, "frames_this_rank": int(b - a)}}
+    if rank == 0 and world == 1 and args.gl_iters > 0:
+        frames = np.array([Tc], dtype=np.int32)
+        wav_out = torch.empty(HOP * (Tc - 1), dtype=torch.float32, device=dev)
+        step = lambda: eng.griffinlim(mag, frames, n_iter=args.gl_iters, momentum=0.0, power=1.2, deemphasis=True, want_trim=True,
+                                      wav_out=wav_out)
+        step()
+        torch.cuda.synchronize()
+        t0.record()
+        step()
+        t1.record()
+        torch.cuda.synchronize()
+        gl_ms = t0.elapsed_time(t1)
+        out["gl_round_trip"] = {"value": secs / (gl_ms * 1e-3), "unit": "audio-s/s", "ms": gl_ms, "iters": args.gl_iters,
+                                "multi_gpu": "replicas only"}
+    return out
 
 
 def run_loader(args, eng, pool, rank):
@@ -552,6 +609,7 @@ def main():
     ap.add_argument("--gl-iters", type=int, default=100)
     ap.add_argument("--gl-steps", type=int, default=3)
     ap.add_argument("--loader-batch", type=int, default=32)
+    ap.add_argument("--longform-seconds", type=int, default=600)
     ap.add_argument("--sample-clips", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -400,3 +400,20 @@ def test_loader_collate_on_the_fly_matches_reference_collate():
     mel2, lens2, names2 = PP.collate_fn_postnet_mel(batch)
     assert names2 == names and lens2 == [so.spectrograms_from_wave(w)[0].shape[0] for w in waves]
     assert np.abs(mel2.cpu().numpy()[0, :lens2[0]] - so.spectrograms_from_wave(waves[0])[0]).max() <= TOL
+
+
+def test_long_form_frame_range_sharding_is_bit_identical():
+    """C5: one long waveform, frames sharded over 'ranks' with a halo (unast_b200.longform): the concatenation of the
+    ranks' frames is bit-identical to the single-GPU result and within the parity gate of the oracle."""
+    from unast_b200 import longform as LF, synth, utils as U
+    w = np.concatenate([synth.speech_like(9.0, 70 + i) for i in range(4)])          # 36 s
+    (mel1, mag1), = U.spectrograms_from_waves([w])
+    for world in (1, 3, 5):
+        parts = [LF.spectrograms_long(w, rank=r, world=world) for r in range(world)]
+        T = parts[0][3]
+        assert [p[2] for p in parts] == LF.frame_ranges(T, world) and T == mel1.shape[0]
+        mel = np.concatenate([p[0] for p in parts], axis=0)
+        mag = np.concatenate([p[1] for p in parts], axis=0)
+        assert np.array_equal(mel, mel1) and np.array_equal(mag, mag1)
+    omel, omag = so.spectrograms_from_wave(w)
+    assert np.abs(mel1 - omel).max() <= TOL and np.abs(mag1 - omag).max() <= TOL

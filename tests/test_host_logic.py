@@ -188,3 +188,22 @@ def test_loader_sort_is_the_reference_permutation():
     assert order == ref == [1, 4, 5, 0, 2, 3, 6] and tl == tlen
     padded = PP._prepare_data([batch[i]["text"] for i in order])
     assert np.array_equal(padded, so._prepare_data([batch[i]["text"] for i in order])) and padded.shape == (7, 9)
+
+
+def test_long_form_chunks_cover_what_their_frames_see():
+    """Frame-range sharding of one long waveform: ranges partition the frames; every kept frame's taps (and the sample
+    before them, for the pre-emphasis) lie inside the chunk unless the chunk edge is the true signal edge."""
+    from unast_b200 import longform as LF
+    for n in (1101, 5000, 275 * 400 + 13, 13_230_000):
+        T = 1 + n // 275
+        for world in (1, 2, 3, 8):
+            rs = LF.frame_ranges(T, world)
+            assert rs[0][0] == 0 and rs[-1][1] == T and all(rs[i][1] == rs[i + 1][0] for i in range(world - 1))
+            for a, b in rs:
+                c0, c1, keep = LF.chunk_for_range(n, a, b)
+                if b <= a:
+                    continue
+                assert c0 % 275 == 0 and keep.start == a - c0 // 275 and keep.stop - keep.start == b - a
+                assert c0 == 0 or 275 * a - 552 >= c0
+                assert c1 == n or 275 * (b - 1) + 551 <= c1 - 1
+                assert 1 + (c1 - c0) // 275 >= keep.stop

@@ -1,7 +1,10 @@
 // K1 (experiment, not the default: -DUNAST_FE64_WS=1): warp-specialised fused mel / magnitude front end (replaces
-// reference src/utils.py:251-276).  Parity-green on B200 but slower than frontend_pf_kernel (45.5 ms vs 40.4 ms on C2,
-// profiles/r1n_ncu_fe_f64_ws.txt): with setmaxnreg the FFT warps get 152 registers instead of 168 and spill (91 local
-// loads per frame), and the leading FFT warps still wait for the slowest warp plus the mel warps' latency.
+// reference src/utils.py:251-276).  Parity-green on B200 but slower than frontend_pf_kernel (40.4 ms on C2) in every
+// configuration tried: 12 + 4 warps with setmaxnreg 45.5 ms (profiles/r1n_ncu_fe_f64_ws.txt: the FFT warps get 152
+// registers instead of 168 and spill, 91 local loads per frame, and the leading FFT warps still wait for the slowest
+// warp plus the mel warps' latency), 60 ms with the wait moved to the end of the frame (more spills); 10 + 2 warps at
+// 168 registers without setmaxnreg 50.4 ms (two mel warps cannot keep up with ten FFT warps: the 3xTF32 contraction
+// is a latency chain of ~6,000 warp instructions per tile).
 //
 // frontend_pf_kernel (frontend_pf.cuh) stops all twelve FFT warps twice per tile: at the CTA barrier that waits for the
 // slowest of them, and during the mel phase, when the FP64 pipe idles (about a quarter of its stall samples,
@@ -23,10 +26,19 @@
 
 namespace unast {
 
-constexpr int WS_FW = 12;                   // FFT warps (three warp groups)
-constexpr int WS_MW = 4;                    // mel warps (one warp group)
+#ifndef UNAST_WS_FW
+#define UNAST_WS_FW 10
+#endif
+#ifndef UNAST_WS_MW
+#define UNAST_WS_MW 2
+#endif
+constexpr int WS_FW = UNAST_WS_FW;          // FFT warps
+constexpr int WS_MW = UNAST_WS_MW;          // mel warps
+// With 12 + 4 warps the register file only works out with setmaxnreg (152 / 56 registers, warp-group granularity);
+// with 10 + 2 every warp keeps the 168 registers of a 12-warp CTA and no reallocation is needed.
+constexpr bool WS_SETREG = (WS_FW + WS_MW) * 32 * 168 > 65536;
 constexpr int WS_REGS_FFT = 152, WS_REGS_MEL = 56;
-static_assert(WS_FW * 32 * WS_REGS_FFT + WS_MW * 32 * WS_REGS_MEL <= 65536, "register file");
+static_assert(!WS_SETREG || (WS_FW % 4 == 0 && WS_MW % 4 == 0 && WS_FW * 32 * WS_REGS_FFT + WS_MW * 32 * WS_REGS_MEL <= 65536), "register file");
 
 template <class T>
 struct FeWsLayout : FePfLayout<T, WS_FW> {
@@ -97,7 +109,7 @@ __global__ void __launch_bounds__((WS_FW + WS_MW) * 32, 1) frontend_ws_kernel(co
 
     if (warp < WS_FW) {
         // ======================================= FFT warps =======================================
-        reg_inc<WS_REGS_FFT>();
+        if constexpr (WS_SETREG) reg_inc<WS_REGS_FFT>();
         T* xs = reinterpret_cast<T*>(smem + L::off_xch + warp * L::XCH_BYTES);
         unsigned char* stage = smem + L::off_stage + warp * PF_STAGE_BYTES;
         auto wp = [&]() {
@@ -138,9 +150,7 @@ __global__ void __launch_bounds__((WS_FW + WS_MW) * 32, 1) frontend_ws_kernel(co
             float* mrow = P.mag_out ? P.mag_out + (size_t)(cur.fbase + t) * NBINS : nullptr;
             // this warp's row may be overwritten once the mel warps are done with the previous tile: checked in the
             // middle of the transform (fewest live registers), normally long satisfied
-            auto rows_free = [&]() { if (it > 0) mbar_wait_inline(bar_empty, (uint32_t)(it - 1) & 1u); };
-            if (live) warp_fft1024_split<T, 18>(v, xs, s_tw, lane, rows_free);
-            else rows_free();
+            if (live) warp_fft1024_split<T, 18>(v, xs, s_tw, lane);
             if (live) {
                 float pa[16], pb[16], p512 = 0.0f;
                 rfft_post_pairs<T>(v, reinterpret_cast<C*>(xs), wp, lane, [&](auto jj, C xa, C xb) {
@@ -150,6 +160,10 @@ __global__ void __launch_bounds__((WS_FW + WS_MW) * 32, 1) frontend_ws_kernel(co
                     pa[j] = fmaf(ar, ar, ai * ai);
                     pb[j] = fmaf(br, br, bi * bi);
                 }, [&](C x) { const float r = (float)x.x, i = (float)x.y; p512 = fmaf(r, r, i * i); });
+                // this warp's row may be overwritten once the mel warps are done with the previous tile: checked here,
+                // at the very end of the frame, where only the 33 powers are live -- the mel warps have had almost a
+                // whole tile time
+                if (it > 0) mbar_wait_inline(bar_empty, (uint32_t)(it - 1) & 1u);
                 float* rowa = row + lane;
                 float* rowb = row + 1024 - lane;
                 static_for<0, 16>([&](auto jj) {
@@ -169,6 +183,9 @@ __global__ void __launch_bounds__((WS_FW + WS_MW) * 32, 1) frontend_ws_kernel(co
                     if (lane == 0) mrow[512] = db_norm_pw_nf(p512);
                 }
             }
+            // a warp without a frame in this tile still has to see `empty` of the previous tile before it arrives, or
+            // it could arrive twice in one phase of `full`
+            if (!live && it > 0) mbar_wait_inline(bar_empty, (uint32_t)(it - 1) & 1u);
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_full);                         // this warp's row of the tile is in place
         }
@@ -176,12 +193,13 @@ __global__ void __launch_bounds__((WS_FW + WS_MW) * 32, 1) frontend_ws_kernel(co
     }
 
     // ======================================= mel warps =======================================
-    reg_dec<WS_REGS_MEL>();
+    if constexpr (WS_SETREG) reg_dec<WS_REGS_MEL>();
     const int mw = warp - WS_FW;
     const int gq = lane >> 2, tq = lane & 3;
     const float* a_lo = rows + gq * ROW_STRIDE + tq;
     const float* a_hi = rows + (gq + 8 < L::NR ? gq + 8 : L::NR - 1) * ROW_STRIDE + tq;   // rows >= R: the zero row
     const uint32_t tbase = *s_tmem + ((uint32_t)(32 * (warp & 3)) << 16);                    // own quadrant, <= 127 pairs
+    static_assert(WS_MW <= 4, "one TMEM lane quadrant per mel warp");
     const int u0 = M.unit_begin[mw], u1 = M.unit_begin[mw + 1];
     {   // this warp's B fragments -> tensor memory, in visiting order, already split for 3xTF32: 4 columns per pair
         int lp = 0;
@@ -218,16 +236,25 @@ __global__ void __launch_bounds__((WS_FW + WS_MW) * 32, 1) frontend_ws_kernel(co
                 mma_tf32(d, ah, __float_as_uint(bq.z), __float_as_uint(bq.w));
                 mma_tf32(d, ah, __float_as_uint(bq.x), __float_as_uint(bq.y));
             };
-            for (int p = un.p0; p < un.p1; p += 2, lp += 2) {
-                float4 b0 = tmem_ld4(tbase + 4 * lp), b1 = tmem_ld4(tbase + 4 * lp + 4);
-                tmem_wait_ld(b0, b1);
+            auto load4 = [&](float4 (&q)[4], int l) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) q[i] = tmem_ld4(tbase + 4 * (l + i));
+            };
+            float4 nb[4];
+            load4(nb, lp);
+            for (int p = un.p0; p < un.p1; p += 4, lp += 4) {
+                tmem_wait_ld(nb[0], nb[1], nb[2], nb[3]);
+                const float4 b0 = nb[0], b1 = nb[1], b2 = nb[2], b3 = nb[3];
+                if (p + 4 < un.p1) load4(nb, lp + 4);
                 pair_ops(s_kb[p], b0, acc[0]);
                 if (p + 1 < un.p1) pair_ops(s_kb[p + 1], b1, acc[1]);
+                if (p + 2 < un.p1) pair_ops(s_kb[p + 2], b2, acc[2]);
+                if (p + 3 < un.p1) pair_ops(s_kb[p + 3], b3, acc[3]);
             }
-            lp -= (un.p1 - un.p0) & 1;                                    // the last chunk may have been partial
+            lp -= (4 - ((un.p1 - un.p0) & 3)) & 3;                        // the last chunk may have been partial
             float s4[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) s4[q] = acc[0][q] + acc[1][q];
+            for (int q = 0; q < 4; ++q) s4[q] = (acc[0][q] + acc[1][q]) + (acc[2][q] + acc[3][q]);
             if (un.split >= 0) {
                 // half of an n-tile: add into the shared tile (two contributions onto zero: order-independent); the
                 // warp that arrives second turns the sum into mel and clears the tile for the next one

@@ -418,7 +418,7 @@ int unast_create(int device, unast_ctx** out) {
     build_coop(8, h_units8, c->coop8);
     build_coop(16, h_units16, c->coop16);
     build_coop(UNAST_FE64_PF ? UNAST_FE64_PF : 8, h_unitsN, c->coopN);
-    build_coop(4, h_units4, c->coop4);
+    build_coop(WS_MW, h_units4, c->coop4);
 
     cudaError_t e = cudaSuccess;
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };

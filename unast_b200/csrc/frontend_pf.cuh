@@ -7,14 +7,16 @@
 // two warps per scheduler, a third of the time in load / epilogue phases that nothing overlapped):
 //
 //   * the transposition goes through a split-plane buffer (real plane, then imaginary plane: 8.5 KB per warp for
-//     float64 instead of 16.5 KB) and the real-FFT post-processing pairs bin k with 1024 - k by warp shuffles, so a
-//     float64 frame needs half the shared memory and half the registers' worth of staging: FW = 12 warps of 168
-//     registers fit one SM (three per scheduler instead of two);
+//     float64 instead of 16.5 KB), which is what lets FW = 12 warps of 168 registers fit one SM (three per scheduler
+//     instead of two);
 //   * the post-processing computes each (k, 1024 - k) pair once: lane l owns its registers j < 16 (bins l + 32 j) and
-//     the mirror bins, fetched from lane 32 - l -- 12 instead of 16 flops per bin pair, half the factor products,
-//     half the shuffles;
+//     their mirrors, which lane 32 - l parks in the idle transposition buffer -- 12 instead of 16 flops per bin pair,
+//     half the factor products, no shuffles, no lane-0 selects;
 //   * the next frame's PCM16 samples are prefetched with cp.async into a warp-private staging buffer while the
-//     current frame is transformed (the global-load latency was fully exposed before).
+//     current frame is transformed (the global-load latency was fully exposed before);
+//   * tile bookkeeping is resolved once per CTA, two tiles ahead, into a ring in shared memory;
+//   * the CTA barrier after the mel phase is replaced by an mbarrier whose wait sits in the middle of the next
+//     transform; split n-tiles are finished by whichever of their two warps arrives second.
 #pragma once
 #include "frontend.cuh"
 

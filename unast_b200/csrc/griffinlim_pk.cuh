@@ -41,10 +41,21 @@ __device__ __forceinline__ void gl_update_bin(float& xr, float& xi, int k, const
         float ar = xr, ai = xi;
         if (!first_iter) { const float2 pr = tp[k]; ar = fmaf(-alpha, pr.x, ar); ai = fmaf(-alpha, pr.y, ai); }
         tp[k] = make_float2(xr, xi);
-        const float sc = s / (sqrtf(fmaf(ar, ar, ai * ai)) + 1e-16f);
+        const float sc = s * rsqrtf(fmaxf(fmaf(ar, ar, ai * ai), 1e-30f));  // librosa: angles / (|angles| + 1e-16)
         xr = ar * sc;
         xi = ai * sc;
     }
+}
+
+// momentum update with the bin's previous estimate already in registers (zero on the first iteration)
+__device__ __forceinline__ void gl_update_bin_m(float& xr, float& xi, int k, const float* __restrict__ srow, float2* tp,
+                                                float alpha, float2 pr) {
+    const float s = srow[k];
+    const float ar = fmaf(-alpha, pr.x, xr), ai = fmaf(-alpha, pr.y, xi);
+    tp[k] = make_float2(xr, xi);
+    const float sc = s * rsqrtf(fmaxf(fmaf(ar, ar, ai * ai), 1e-30f));
+    xr = ar * sc;
+    xi = ai * sc;
 }
 
 template <bool MOMENTUM>
@@ -86,6 +97,14 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
     for (int c = lane; c < S_STRIDE / 4; c += 32) cp_async16(srow + 4 * c, P.S + (size_t)f0 * S_STRIDE + 4 * c);
     cp_async_commit();
     if (P.mode == GL_ITER) asm volatile("griddepcontrol.wait;" ::: "memory");   // the previous iteration is complete
+    // momentum: pull a frame's previous estimate (8,200 bytes) into L2 one frame before its bins are read
+    auto prefetch_prev = [&](int f) {
+        if (MOMENTUM && P.mode == GL_ITER && !P.first_iter) {
+            const char* row = reinterpret_cast<const char*>(P.tprev + (size_t)f * NBINS);
+            for (int c = lane; c < (NBINS * 8 + 127) / 128; c += 32) prefetch_l2(row + 128 * c);
+        }
+    };
+    prefetch_prev(f0);
 
     for (int f = f0; f < f1; ++f) {
         if (f >= P.frame_off[b + 1]) { while (f >= P.frame_off[b + 1]) ++b; have_carry = false; }
@@ -108,6 +127,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
             __syncwarp();
         }
 
+        if (f + 1 < f1) prefetch_prev(f + 1);
         Pk v;
         if (P.mode == GL_ITER) {
             // ---- 1. previous iteration's signal: normalise, reflect-pad, window (layout A) ----
@@ -194,19 +214,46 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
         __syncwarp();
         float2* tp = MOMENTUM ? P.tprev + (size_t)f * NBINS : nullptr;
         float x512r = 0.f, x512i = 0.f;                                  // lane 0: bin 512, its own mirror
-        if (P.mode == GL_ITER) {
+        if (P.mode == GL_ITER && MOMENTUM) {
+            // The previous estimates are loaded one group of four bins ahead of the group being updated: a load that
+            // follows a store to the same array in program order cannot be hoisted above it, so without this every
+            // bin would wait for its own round trip to HBM (33 x 4 serialised misses per frame).
+            const bool prev = !P.first_iter;
+            float2 pr[4] = {}, p2[4] = {};
+            auto load4 = [&](float2 (&d)[4], int ka) { d[0] = tp[ka]; d[1] = tp[ka + 32]; d[2] = tp[1024 - ka]; d[3] = tp[992 - ka]; };
+            if (prev) { load4(pr, lane); load4(p2, lane + 64); }
+            float2 p512 = make_float2(0.f, 0.f);
+            if (prev && lane == 0) p512 = tp[512];
             static_for<0, 8>([&](auto mm) {
                 constexpr int m = decltype(mm)::value;
                 const int ka = lane + 64 * m;
-                gl_update_bin<MOMENTUM>(v.re[m].x, v.im[m].x, ka, srow, tp, P.alpha, P.first_iter);
-                gl_update_bin<MOMENTUM>(v.re[m].y, v.im[m].y, ka + 32, srow, tp, P.alpha, P.first_iter);
-                gl_update_bin<MOMENTUM>(v.re[m + 8].x, v.im[m + 8].x, 1024 - ka, srow, tp, P.alpha, P.first_iter);
-                gl_update_bin<MOMENTUM>(v.re[m + 8].y, v.im[m + 8].y, 992 - ka, srow, tp, P.alpha, P.first_iter);
+                float2 nx[4] = {};
+                if (m < 6 && prev) load4(nx, ka + 128);
+                gl_update_bin_m(v.re[m].x, v.im[m].x, ka, srow, tp, P.alpha, pr[0]);
+                gl_update_bin_m(v.re[m].y, v.im[m].y, ka + 32, srow, tp, P.alpha, pr[1]);
+                gl_update_bin_m(v.re[m + 8].x, v.im[m + 8].x, 1024 - ka, srow, tp, P.alpha, pr[2]);
+                gl_update_bin_m(v.re[m + 8].y, v.im[m + 8].y, 992 - ka, srow, tp, P.alpha, pr[3]);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { pr[i] = p2[i]; p2[i] = nx[i]; }
+            });
+            if (lane == 0) {
+                x512r = 2.0f * xs[32 * PK_PARK_S + 16];
+                x512i = -2.0f * xs[PK_PARK_PLANE + 32 * PK_PARK_S + 16];
+                gl_update_bin_m(x512r, x512i, 512, srow, tp, P.alpha, p512);
+            }
+        } else if (P.mode == GL_ITER) {
+            static_for<0, 8>([&](auto mm) {
+                constexpr int m = decltype(mm)::value;
+                const int ka = lane + 64 * m;
+                gl_update_bin<false>(v.re[m].x, v.im[m].x, ka, srow, tp, P.alpha, P.first_iter);
+                gl_update_bin<false>(v.re[m].y, v.im[m].y, ka + 32, srow, tp, P.alpha, P.first_iter);
+                gl_update_bin<false>(v.re[m + 8].x, v.im[m + 8].x, 1024 - ka, srow, tp, P.alpha, P.first_iter);
+                gl_update_bin<false>(v.re[m + 8].y, v.im[m + 8].y, 992 - ka, srow, tp, P.alpha, P.first_iter);
             });
             if (lane == 0) {
                 x512r = 2.0f * xs[32 * PK_PARK_S + 16];                  // X[512] = 2 conj(z), z parked by pk_post_pairs
                 x512i = -2.0f * xs[PK_PARK_PLANE + 32 * PK_PARK_S + 16];
-                gl_update_bin<MOMENTUM>(x512r, x512i, 512, srow, tp, P.alpha, P.first_iter);
+                gl_update_bin<false>(x512r, x512i, 512, srow, tp, P.alpha, P.first_iter);
             }
         } else {
             // initial spectrum S * angles0 in the shifted frame

@@ -509,10 +509,47 @@ def run_loader(args, eng, pool, rank):
     torch.cuda.synchronize()
     ms = t0.elapsed_time(t1) / n
     audio_s = float(HOP * (ml.numpy() - 1).sum()) / SR
+    # next row (8(f) rank 2): specaugment + noise_fn on that batch (train.py:236, network.py:205), and the masking
+    # kernel against HBM on a batch large enough to leave the latency regime (its roofline: read + write 4 B/element,
+    # plus one more read for the slab mean)
+    from unast_b200 import augment as AUG
+    for _ in range(3):
+        aug = AUG.specaugment_noise(mel, ml)
+    torch.cuda.synchronize()
+    t0.record()
+    for _ in range(n):
+        aug = AUG.specaugment_noise(mel, ml)
+    t1.record()
+    torch.cuda.synchronize()
+    aug_ms = t0.elapsed_time(t1) / n
+    Bb, Tb = 1024, 800
+    big = torch.rand((Bb, Tb, 80), device=mel.device)
+    big_out = torch.empty_like(big)
+    spans = torch.from_numpy(np.tile(np.array([[5, 19, 100, 99]], np.int32), (Bb, 1))).to(mel.device)
+    keep = (torch.rand((Bb, Tb), device=mel.device) > 0.3).float()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=mel.device)
+    tot = 0.0
+    for r in range(6):
+        flush.zero_()
+        t0.record()
+        eng.mel_augment(big, spans=spans, keep=keep, out=big_out)
+        t1.record()
+        torch.cuda.synchronize()
+        if r:
+            tot += t0.elapsed_time(t1)
+    big_ms = tot / 5
+    alg = 12.0 * big.numel()
+    peak = measured_peaks()[0]["hbm_gbs"]
+    del big, big_out, flush
     return {"workload": "C4 (BASELINE.json configs[3]): collate_fn_transformer with on-the-fly mels, batch %d, PCM16 host -> "
                         "[%d, %d, 80] float32 device tensor" % (B, B, int(mel.shape[1])),
             "e2e": {"value": audio_s / (ms * 1e-3), "unit": "audio-s/s", "ms_per_batch": ms,
                     "h2d_bytes_per_step": int(2 * lens.sum()), "d2h_bytes_per_step": int(8 * B + 4 * (B + 1))},
+            "augment": {"workload": "specaugment + noise_fn in one pass (unast_mel_augment), host draws included",
+                        "ms_per_batch": aug_ms,
+                        "kernel": {"workload": "[%d, %d, 80] float32, spans + keep mask, L2 flushed between launches" % (Bb, Tb),
+                                   "ms": big_ms, "algorithmic_bytes": alg, "achieved_gbps": alg / (big_ms * 1e-3) / 1e9,
+                                   "peak_gbps": peak, "frac": (alg / (big_ms * 1e-3) / 1e9 / peak) if peak else None}},
             "note": "latency regime: one 32-utterance batch is ~15 k frames, a tenth of what fills the GPU"}
 
 

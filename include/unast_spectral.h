@@ -107,6 +107,21 @@ int unast_griffinlim(unast_ctx* ctx, const float* mag_norm, const int32_t* frame
                      float momentum, const float* angles0, float power, int deemphasis, float* wav_out,
                      int32_t* bounds_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- next row: the masking ops applied to the padded mel batch ----------- */
+
+/* utils.specaugment (utils.py:51-75, called at train.py:236) and utils.noise_fn (utils.py:40-49, called at
+ * network.py:205,307) on a float[B][T][D] batch, in one pass:
+ *     out[b][t][:] = (t in [f_zero, f_zero+f) or t in [t_zero, t_zero+t) ? fill_b : x[b][t][:]) * keep[b][t]
+ * spans: device int32 [B][4] = {f_zero, f, t_zero, t} as the reference draws them (both spans run along the TIME
+ *        axis: `res[i][:][a:b]` slices rows), or NULL for no spans; fill_b = mean of the whole padded slab x[b]
+ *        (utils.py:59), or 0 if replace_with_zero.
+ * keep:  device float [B][T] = the reference's `zero_mask` (torch.bernoulli(1 - mask_p)), or NULL.
+ * out may alias x only when spans is NULL or replace_with_zero (the mean is read from x).
+ * workspace >= unast_mel_augment_workspace_bytes(B) (partial sums of the mean). */
+size_t unast_mel_augment_workspace_bytes(int B);
+int unast_mel_augment(unast_ctx* ctx, const float* x, int B, int T, int D, const int32_t* spans, const float* keep,
+                      int replace_with_zero, float* out, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- diagnostics (used by the test-suite to pin the FFT core on its own) --------------------- */
 
 /* frames: float[F][2048] whose samples [1102, 2048) are zero; out: complex64[F][1025] = rfft(frame). */

@@ -375,3 +375,43 @@ def loader_items_from_waves(texts, waves, fnames=None):
             d["fname"] = fnames[i]
         items.append(d)
     return items
+
+
+# ---- next row: src/utils.py:40-75, specaugment / noise_fn ------------------------------------
+# PINNED: tests/golden/make_augment_golden.py runs the reference's own two functions (torch only) and commits their
+# outputs as tests/golden/augment.npz; tests/test_oracle_golden.py checks this restatement against them bit for bit.
+def specaugment_spans(mel_len, freq_mask=20, time_mask=100):
+    """The random draws of utils.specaugment (utils.py:55-68), in its order: torch.randint for the span lengths of the
+    whole batch, then random.randrange per utterance.  Returns int32 [B, 4] rows (f_zero, f, t_zero, t)."""
+    import random
+    import torch
+    mel_len = torch.as_tensor(np.asarray(mel_len))
+    freq_len = torch.randint(0, freq_mask, mel_len.shape)                   # utils.py:55
+    time_len = torch.randint(0, time_mask, mel_len.shape)                   # utils.py:56
+    spans = np.zeros((mel_len.shape[0], 4), np.int32)
+    for i in range(freq_len.shape[0]):
+        n = int(mel_len[i])
+        f, t = int(freq_len[i]), int(time_len[i])
+        if n - t <= 0:                                                      # utils.py:63-65
+            t = random.randrange(0, n // 2)
+        f_zero = random.randrange(0, n - f)                                 # utils.py:66
+        t_zero = random.randrange(0, n - t)                                 # utils.py:67
+        spans[i] = (f_zero, f, t_zero, t)
+    return spans
+
+
+def specaugment_apply(mel, spans, replace_with_zero=False):
+    """utils.py:58-73 given the draws: mean of the padded slab first, then two ROW spans (``res[i][:][a:b]`` slices the
+    time axis) filled with it (or 0).  float32 throughout; the mean is numpy's pairwise float32 sum / count, which
+    torch's float32 mean matches to rounding (the golden test allows 1 ulp of the fill value)."""
+    res = np.array(mel, dtype=np.float32, copy=True)
+    for i, (f_zero, f, t_zero, t) in enumerate(np.asarray(spans)):
+        fill = np.float32(0.0) if replace_with_zero else res[i].mean(dtype=np.float32)
+        res[i, f_zero:f_zero + f, :] = fill
+        res[i, t_zero:t_zero + t, :] = fill
+    return res
+
+
+def noise_apply(to_noise, zero_mask):
+    """utils.py:46-49 given the Bernoulli draw: ``to_noise * zero_mask.unsqueeze(-1)``."""
+    return np.asarray(to_noise, np.float32) * np.asarray(zero_mask, np.float32)[..., None]

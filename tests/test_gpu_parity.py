@@ -417,3 +417,91 @@ def test_long_form_frame_range_sharding_is_bit_identical():
         assert np.array_equal(mel, mel1) and np.array_equal(mag, mag1)
     omel, omag = so.spectrograms_from_wave(w)
     assert np.abs(mel1 - omel).max() <= TOL and np.abs(mag1 - omag).max() <= TOL
+
+
+# ------------------------------------------------------------------------------------------------
+# next row: specaugment / noise_fn on the padded mel batch
+# ------------------------------------------------------------------------------------------------
+def _seed_all(seed):
+    import random
+    torch = _torch()
+    torch.manual_seed(int(seed))
+    random.seed(int(seed))
+
+
+def test_specaugment_matches_reference_output(golden):
+    """Same seeds as the fixture: the drop-in must mask the reference's rows with the reference's fill value."""
+    torch = _torch()
+    from unast_b200.augment import specaugment
+    g = golden("augment")
+    mel = torch.from_numpy(g["mel"]).cuda()
+    keep = mel.clone()
+    for key, rz in (("sa_mean", False), ("sa_zero", True)):
+        _seed_all(g["seed"])
+        out = specaugment(mel, torch.from_numpy(g["mel_len"]), replace_with_zero=rz)
+        assert out.data_ptr() != mel.data_ptr() and torch.equal(mel, keep)        # a clone; the input is untouched
+        out = out.cpu().numpy()
+        assert np.array_equal(out != g["mel"], g[key] != g["mel"])
+        assert np.abs(out - g[key]).max() <= (0.0 if rz else 6e-8)
+    _seed_all(g["seed"])
+    with pytest.raises(ValueError):                                              # utils.py:66 on a too-short utterance
+        specaugment(mel[:, :10].contiguous(), torch.full((6,), 10, dtype=torch.int64))
+
+
+def test_noise_fn_matches_reference_formula_on_the_device_stream():
+    torch = _torch()
+    from unast_b200.augment import noise_fn
+    rng = np.random.RandomState(11)
+    for shape in ((5, 77, 80), (3, 50, 257), (2, 9, 3)):                        # float4 path and the scalar path
+        x = torch.from_numpy(rng.randn(*shape).astype(np.float32)).cuda()
+        torch.manual_seed(99)
+        out = noise_fn(x, mask_p=.3)
+        torch.manual_seed(99)                                                    # utils.py:46-49, same generator
+        gen = torch.zeros(shape[:2], device=x.device).fill_(1 - .3)
+        want = x * torch.bernoulli(gen).unsqueeze(-1)
+        assert torch.equal(out, want)
+    dropped = (out.abs().sum(-1) == 0).float().mean().item()
+    assert 0.0 <= dropped <= 1.0
+
+
+def test_mel_augment_large_batch_against_oracle(engine):
+    """Ragged batch at loader scale, spans + keep mask in one pass, against the oracle's row arithmetic."""
+    torch = _torch()
+    rng = np.random.RandomState(5)
+    B, T, D = 37, 811, 80
+    lens = rng.randint(300, T + 1, size=B)
+    lens[0] = T
+    x = rng.uniform(0.0, 1.0, size=(B, T, D)).astype(np.float32)
+    for i, n in enumerate(lens):
+        x[i, n:] = 0.0
+    _seed_all(3)
+    spans = so.specaugment_spans(lens)
+    keep = (rng.rand(B, T) > 0.3).astype(np.float32)
+    want = so.noise_apply(so.specaugment_apply(x, spans), keep)
+    xd = torch.from_numpy(x).cuda()
+    got = engine.mel_augment(xd, spans=torch.from_numpy(spans).cuda(), keep=torch.from_numpy(keep).cuda()).cpu().numpy()
+    assert np.abs(got - want).max() <= 6e-8
+    assert np.array_equal(got == 0, want == 0)
+    # determinism of the two-stage mean, and in-place operation where it is allowed
+    again = engine.mel_augment(xd, spans=torch.from_numpy(spans).cuda(), keep=torch.from_numpy(keep).cuda()).cpu().numpy()
+    assert np.array_equal(got, again)
+    z = xd.clone()
+    engine.mel_augment(z, spans=torch.from_numpy(spans).cuda(), replace_with_zero=True, out=z)
+    assert np.array_equal(z.cpu().numpy(), so.specaugment_apply(x, spans, replace_with_zero=True))
+    with pytest.raises(Exception):
+        engine.mel_augment(xd, spans=torch.from_numpy(spans).cuda(), out=xd)   # the mean is read from x
+
+
+def test_loader_batch_then_specaugment_like_the_supervised_step():
+    """collate_fn_transformer -> specaugment(mel, mel_len) (train.py:232-236) without leaving the device."""
+    torch = _torch()
+    from unast_b200 import preprocess, synth
+    from unast_b200.augment import specaugment
+    items = [{"text": np.arange(3 + i), "wave": synth.speech_like(1.6 + 0.2 * i, 60 + i)} for i in range(4)]
+    text, mel, text_len, mel_len = preprocess.collate_fn_transformer(items)
+    _seed_all(8)
+    aug = specaugment(mel, mel_len)
+    _seed_all(8)
+    spans = so.specaugment_spans(mel_len.cpu().numpy())
+    want = so.specaugment_apply(mel.cpu().numpy(), spans)
+    assert np.abs(aug.cpu().numpy() - want).max() <= 6e-8

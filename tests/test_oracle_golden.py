@@ -112,3 +112,51 @@ def test_deemphasis_inverts_preemphasis():
     y = rng.randn(5000)
     pre = np.append(y[0], y[1:] - 0.97 * y[:-1])
     assert np.abs(so.deemphasis(pre) - y).max() < 1e-9
+
+
+# ---- next row: specaugment / noise_fn (src/utils.py:40-75), pinned on the reference's own output ----
+def _seed(seed):
+    import random
+    import torch
+    torch.manual_seed(int(seed))
+    random.seed(int(seed))
+
+
+def test_specaugment_restatement_matches_reference_output(golden):
+    g = golden("augment")
+    for key, rz in (("sa_mean", False), ("sa_zero", True)):
+        _seed(g["seed"])
+        spans = so.specaugment_spans(g["mel_len"])
+        out = so.specaugment_apply(g["mel"], spans, replace_with_zero=rz)
+        changed = out != g["mel"]
+        assert np.array_equal(changed, g[key] != g["mel"])                      # the same rows are masked
+        assert np.array_equal(out[~changed], g[key][~changed])
+        if rz:
+            assert np.array_equal(out, g[key])
+        else:
+            assert np.abs(out - g[key]).max() <= 6e-8                            # 1 ulp of a fill value near 0.5
+    # both spans run along the time axis (whole rows), as `res[i][:][a:b]` does
+    rows = (g["sa_zero"] != g["mel"]).any(axis=2)
+    assert np.array_equal(rows[..., None] & (g["mel"] != 0), g["sa_zero"] != g["mel"])
+
+
+def test_noise_fn_restatement_matches_reference_output(golden):
+    g = golden("augment")
+    assert np.array_equal(so.noise_apply(g["mel"], g["noise_mask"]), g["noise"])
+    assert 0.2 < 1.0 - g["noise_mask"].mean() < 0.4                              # mask_p = .3
+
+
+def test_specaugment_host_draws_and_error_match_reference(golden):
+    from unast_b200.augment import draw_specaugment_spans
+    g = golden("augment")
+    _seed(g["seed"])
+    want = so.specaugment_spans(g["mel_len"])
+    _seed(g["seed"])
+    assert np.array_equal(draw_specaugment_spans(g["mel_len"]), want)
+    import torch
+    _seed(g["seed"])
+    assert np.array_equal(draw_specaugment_spans(torch.from_numpy(g["mel_len"])), want)
+    _seed(g["seed"])
+    with pytest.raises(ValueError) as e:
+        draw_specaugment_spans(np.full(6, 10))
+    assert "ValueError: %s" % e.value == str(g["short_error"])

@@ -33,6 +33,8 @@ SYMBOLS = [
     ("unast_frontend", _i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _sz, _vp]),
     ("unast_griffinlim_workspace_bytes", _sz, [_vp, _i, _f]),
     ("unast_griffinlim", _i, [_vp, _vp, _vp, _i, _i, _f, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp]),
+    ("unast_mel_augment_workspace_bytes", _sz, [_i]),
+    ("unast_mel_augment", _i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
     ("unast_debug_rfft", _i, [_vp, _vp, _i, _i, _vp, _vp]),
     ("unast_debug_irfft", _i, [_vp, _vp, _i, _vp, _vp]),
     ("unast_debug_pipe_peak", _i, [_vp, _i, _i, _vp, C.POINTER(C.c_double), _vp]),

@@ -15,6 +15,7 @@
 #include "griffinlim.cuh"
 #include "griffinlim_pk.cuh"
 #include "trim.cuh"
+#include "augment.cuh"
 
 using namespace unast;
 
@@ -689,6 +690,33 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
 }
 
 // ---- diagnostics ----
+// ---- masking ops on the padded mel batch (8(f) rank 2) ----
+size_t unast_mel_augment_workspace_bytes(int B) { return B > 0 ? align256((size_t)B * AUG_PARTS * sizeof(double)) : 0; }
+
+int unast_mel_augment(unast_ctx* c, const float* x, int B, int T, int D, const int32_t* spans, const float* keep,
+                      int replace_with_zero, float* out, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!c || !x || !out || B <= 0 || T <= 0 || D <= 0) return fail(UNAST_E_ARG, "unast_mel_augment: bad argument");
+    if (B > 65535) return fail(UNAST_E_ARG, "unast_mel_augment: B must be <= 65535");
+    const bool need_mean = spans && !replace_with_zero;
+    if (need_mean && x == out) return fail(UNAST_E_ARG, "unast_mel_augment: in-place needs replace_with_zero or no spans");
+    if (need_mean && (!workspace || workspace_bytes < unast_mel_augment_workspace_bytes(B)))
+        return fail(UNAST_E_WORKSPACE, "unast_mel_augment: workspace too small");
+    if (spans && ((uintptr_t)spans & 15)) return fail(UNAST_E_ARG, "unast_mel_augment: spans must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long slab = (long long)T * D;
+    double* parts = (double*)workspace;
+    if (need_mean) aug_sum_kernel<<<dim3(AUG_PARTS, B), AUG_THREADS, 0, st>>>(x, slab, parts);
+    // enough CTAs per utterance to fill the machine a few times over, at least 8 float4 per thread
+    long long per = (slab / 4 + AUG_THREADS * 8 - 1) / (AUG_THREADS * 8);
+    const long long want = ((long long)c->num_sms * 8 + B - 1) / B;
+    if (per > want) per = want;
+    if (per < 1) per = 1;
+    aug_apply_kernel<<<dim3((unsigned)per, B), AUG_THREADS, 0, st>>>(x, out, T, D, spans, keep, need_mean ? parts : nullptr,
+                                                                     replace_with_zero);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
 int unast_debug_rfft(unast_ctx* c, const float* frames, int F, int precision, float* out, void* stream) {
     if (!c || !frames || !out || F <= 0) return fail(UNAST_E_ARG, "unast_debug_rfft: bad argument");
     cudaStream_t st = (cudaStream_t)stream;

@@ -157,6 +157,25 @@ class SpectralEngine:
         self.launches += 3 + int(n_iter) + (2 if want_trim else 0)
         return wav_out, wav_off, bounds
 
+    def mel_augment(self, x, spans=None, keep=None, replace_with_zero=False, out=None):
+        """utils.py:40-75 on a float32 [B, T, D] device batch: row spans (int32 [B, 4] = f_zero, f, t_zero, t) filled
+        with the slab mean (or 0) and rows scaled by `keep` (float32 [B, T]); one pass, see csrc/augment.cuh."""
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.dim() != 3:
+            raise TypeError("x must be a contiguous float32 [B, T, D] tensor")
+        B, T, D = (int(v) for v in x.shape)
+        if spans is not None and (spans.dtype != torch.int32 or tuple(spans.shape) != (B, 4) or not spans.is_contiguous()):
+            raise TypeError("spans must be a contiguous int32 [B, 4] tensor")
+        if keep is not None and (keep.dtype != torch.float32 or tuple(keep.shape) != (B, T) or not keep.is_contiguous()):
+            raise TypeError("keep must be a contiguous float32 [B, T] tensor")
+        if out is None:
+            out = torch.empty_like(x)
+        nbytes = self.lib.unast_mel_augment_workspace_bytes(B)
+        ws = self._workspace("aug", nbytes)
+        L.check(self.lib.unast_mel_augment(self.h, _ptr(x), B, T, D, _ptr(spans), _ptr(keep), 1 if replace_with_zero else 0,
+                                           _ptr(out), _ptr(ws), nbytes, self._stream()))
+        self.launches += 2 if (spans is not None and not replace_with_zero) else 1
+        return out
+
     # -- diagnostics -------------------------------------------------------------------------------
     def debug_rfft(self, frames, precision="f32"):
         F = frames.shape[0]

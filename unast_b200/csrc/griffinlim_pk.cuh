@@ -47,6 +47,14 @@ __device__ __forceinline__ void gl_update_bin(float& xr, float& xi, int k, const
     }
 }
 
+// classic update of two bins held as a register pair (same arithmetic per half as gl_update_bin<false>)
+__device__ __forceinline__ void gl_update_pair(float2& xr, float2& xi, float sx, float sy) {
+    const float2 pw = __ffma2_rn(xr, xr, __fmul2_rn(xi, xi));
+    const float2 sc = __fmul2_rn(make_float2(sx, sy), make_float2(rsqrtf(fmaxf(pw.x, 1e-16f)), rsqrtf(fmaxf(pw.y, 1e-16f))));
+    xr = __fmul2_rn(xr, sc);
+    xi = __fmul2_rn(xi, sc);
+}
+
 // momentum update with the bin's previous estimate already in registers (zero on the first iteration)
 __device__ __forceinline__ void gl_update_bin_m(float& xr, float& xi, int k, const float* __restrict__ srow, float2* tp,
                                                 float alpha, float2 pr) {
@@ -245,10 +253,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
             static_for<0, 8>([&](auto mm) {
                 constexpr int m = decltype(mm)::value;
                 const int ka = lane + 64 * m;
-                gl_update_bin<false>(v.re[m].x, v.im[m].x, ka, srow, tp, P.alpha, P.first_iter);
-                gl_update_bin<false>(v.re[m].y, v.im[m].y, ka + 32, srow, tp, P.alpha, P.first_iter);
-                gl_update_bin<false>(v.re[m + 8].x, v.im[m + 8].x, 1024 - ka, srow, tp, P.alpha, P.first_iter);
-                gl_update_bin<false>(v.re[m + 8].y, v.im[m + 8].y, 992 - ka, srow, tp, P.alpha, P.first_iter);
+                gl_update_pair(v.re[m], v.im[m], srow[ka], srow[ka + 32]);
+                gl_update_pair(v.re[m + 8], v.im[m + 8], srow[1024 - ka], srow[992 - ka]);
             });
             if (lane == 0) {
                 x512r = 2.0f * xs[32 * PK_PARK_S + 16];                  // X[512] = 2 conj(z), z parked by pk_post_pairs
@@ -303,6 +309,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
         // ---- 5. window, overlap-add with the carried partial sums, emit what became final ----
         // tap i of this frame sits at ola_w[pos0 + i]; taps [0, 275) are complete once this frame is added
         // (given the carry), taps [275, 1102) become the next frame's carry [0, 827).
+        float* wdst = P.ola_w + pos0;
+        const int nseam = (int)max(0LL, min((long long)HOP, seam_end - pos0));   // leading taps shared with the previous run
         static_for<0, 18>([&](auto jj) {
             constexpr int j = decltype(jj)::value;
             const int n = lane + 32 * j;
@@ -317,9 +325,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
                 }
                 auto put = [&](int i, float val) {
                     if (i < HOP) {
-                        const long long q = pos0 + i;
-                        if (q < seam_end) atomicAdd(P.ola_w + q, val);
-                        else P.ola_w[q] = val;
+                        if (i < nseam) atomicAdd(wdst + i, val);
+                        else wdst[i] = val;
                     } else {
                         cb[i - HOP] = val;
                     }

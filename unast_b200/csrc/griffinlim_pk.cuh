@@ -223,32 +223,49 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
         float2* tp = MOMENTUM ? P.tprev + (size_t)f * NBINS : nullptr;
         float x512r = 0.f, x512i = 0.f;                                  // lane 0: bin 512, its own mirror
         if (P.mode == GL_ITER && MOMENTUM) {
-            // The previous estimates are loaded one group of four bins ahead of the group being updated: a load that
-            // follows a store to the same array in program order cannot be hoisted above it, so without this every
-            // bin would wait for its own round trip to HBM (33 x 4 serialised misses per frame).
+            // The previous estimates (8.2 KB per frame) stream through a four-slot ring in the idle transposition
+            // buffer with cp.async, four groups of 4 x 32 bins ahead of the group being updated: register loads that
+            // follow stores to the same array in program order cannot be hoisted, so they would put one L2 / HBM
+            // round trip per group (per bin, unpipelined) on the critical path.  Every lane reads back only what it
+            // copied itself, so cp.async.wait_group is all the synchronisation the ring needs.
             const bool prev = !P.first_iter;
-            float2 pr[4] = {}, p2[4] = {};
-            auto load4 = [&](float2 (&d)[4], int ka) { d[0] = tp[ka]; d[1] = tp[ka + 32]; d[2] = tp[1024 - ka]; d[3] = tp[992 - ka]; };
-            if (prev) { load4(pr, lane); load4(p2, lane + 64); }
+            if (lane == 0) {                                             // bin 512 sits in the park rows the ring reuses
+                x512r = 2.0f * xs[32 * PK_PARK_S + 16];
+                x512i = -2.0f * xs[PK_PARK_PLANE + 32 * PK_PARK_S + 16];
+            }
             float2 p512 = make_float2(0.f, 0.f);
             if (prev && lane == 0) p512 = tp[512];
+            __syncwarp();
+            float2* ring = reinterpret_cast<float2*>(xs) + lane;        // [4 slots][4 rows][32 lanes]
+            auto issue = [&](int m) {
+                if (prev) {
+                    float2* d = ring + (m & 3) * 128;
+                    const int ka = lane + 64 * m;
+                    cp_async8(d, tp + ka);
+                    cp_async8(d + 32, tp + ka + 32);
+                    cp_async8(d + 64, tp + 1024 - ka);
+                    cp_async8(d + 96, tp + 992 - ka);
+                }
+                cp_async_commit();
+            };
+            issue(0); issue(1); issue(2); issue(3);
             static_for<0, 8>([&](auto mm) {
                 constexpr int m = decltype(mm)::value;
                 const int ka = lane + 64 * m;
-                float2 nx[4] = {};
-                if (m < 6 && prev) load4(nx, ka + 128);
+                cp_async_wait_group<(m < 5 ? 3 : 7 - m)>();
+                float2 pr[4] = {};
+                if (prev) {
+                    const float2* d = ring + (m & 3) * 128;
+                    pr[0] = d[0]; pr[1] = d[32]; pr[2] = d[64]; pr[3] = d[96];
+                }
                 gl_update_bin_m(v.re[m].x, v.im[m].x, ka, srow, tp, P.alpha, pr[0]);
                 gl_update_bin_m(v.re[m].y, v.im[m].y, ka + 32, srow, tp, P.alpha, pr[1]);
                 gl_update_bin_m(v.re[m + 8].x, v.im[m + 8].x, 1024 - ka, srow, tp, P.alpha, pr[2]);
                 gl_update_bin_m(v.re[m + 8].y, v.im[m + 8].y, 992 - ka, srow, tp, P.alpha, pr[3]);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) { pr[i] = p2[i]; p2[i] = nx[i]; }
+                if (m < 4) issue(m + 4);                                 // the slot's values are in registers by now
             });
-            if (lane == 0) {
-                x512r = 2.0f * xs[32 * PK_PARK_S + 16];
-                x512i = -2.0f * xs[PK_PARK_PLANE + 32 * PK_PARK_S + 16];
-                gl_update_bin_m(x512r, x512i, 512, srow, tp, P.alpha, p512);
-            }
+            if (lane == 0) gl_update_bin_m(x512r, x512i, 512, srow, tp, P.alpha, p512);
+            __syncwarp();                                                // ring reads done before the park rows are rewritten
         } else if (P.mode == GL_ITER) {
             static_for<0, 8>([&](auto mm) {
                 constexpr int m = decltype(mm)::value;

@@ -114,13 +114,19 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_pk_kernel(const GlParams 
     };
     prefetch_prev(f0);
 
+    // the utterance's frame range and padded base stay in registers; reloaded only when the run crosses into the next one
+    int fbase = P.frame_off[b], fend = P.frame_off[b + 1];
+    long long ubase = P.pad_off[b];
     for (int f = f0; f < f1; ++f) {
-        if (f >= P.frame_off[b + 1]) { while (f >= P.frame_off[b + 1]) ++b; have_carry = false; }
-        const int fbase = P.frame_off[b];
-        const int Tb = P.frame_off[b + 1] - fbase;
+        if (f >= fend) {
+            do { ++b; fend = P.frame_off[b + 1]; } while (f >= fend);
+            fbase = P.frame_off[b];
+            ubase = P.pad_off[b];
+            have_carry = false;
+        }
+        const int Tb = fend - fbase;
         const int t = f - fbase;
         const int L = HOP * (Tb - 1);
-        const long long ubase = P.pad_off[b];
         const long long pos0 = ubase + HOP * t + WIN_LPAD;             // padded index of the frame's tap 0
         const bool last_of_utt = t == Tb - 1;
         const bool last_of_run = f == f1 - 1;

@@ -1,0 +1,189 @@
+// K1 (autonomous): the fused front end of frontend_pf.cuh with NO CTA-wide phase (reference src/utils.py:251-276).
+//
+// frontend_pf_kernel ends every tile of 12 frames in a CTA barrier and a tensor-core mel phase during which the FP64
+// pipe idles (profiles/r1m_ncu_fe_f64.txt: 32 % of the samples, 27 % of them barrier stalls, 693 warp instructions per
+// frame of tile bookkeeping, fragment splitting and mma.sync).  Here every warp owns a contiguous run of frames (an
+// equal share of all frames, located by one binary search) and finishes each frame alone:
+//     samples (cp.async prefetch) -> window -> float64 FFT -> |X| row in its own shared-memory row -> mag row out
+//     -> filterbank from that row in plain FP32 FMAs -> 80 mels out
+// so warps drift apart and one warp's filterbank / epilogue overlaps the others' FP64 transforms.
+//
+// Filterbank without tensor cores: the 80 x 1025 Slaney matrix has 2,001 non-zeros in contiguous runs of 2..83 bins per
+// mel.  The host cuts every run into ITEMS of 8 bins starting at a multiple of 4 (zero weights pad the ends), deals
+// them to (round, lane) slots and lays their weights out so that one item is two 128-bit loads of |X|, two of weights
+// and 8 FMAs.  A mel is the sum of its items' partial sums, added in item order (fixed: deterministic).  About 300
+// items -> 10 rounds per frame.
+#pragma once
+#include "frontend_pf.cuh"
+
+namespace unast {
+
+constexpr int AU_ROW = 1032;                 // floats per |X| row: bins 0..1024 + zero padding up to the last item's end
+constexpr int AU_MAX_ROUNDS = 12;
+
+struct MelItems {                            // device arrays, built once on the host (unast_spectral.cu)
+    const float4* w;                         // [rounds][2][32]: weights of bins k0..k0+3 / k0+4..k0+7 of slot (round, lane)
+    const int* k0;                           // [rounds][32]: first bin of the slot's item (multiple of 4); idle slots: 0, weights 0
+    const int2* mel;                         // [80]: (first item id = round * 32 + lane, number of items)
+    int rounds;
+};
+
+template <class T, int FW>
+struct FeAuLayout {
+    using C = cplx_t<T>;
+    static constexpr bool WP_TABLE = sizeof(T) == 4;
+    static constexpr int XCH_BYTES = (xs_bytes<T>() > WIN * 4 ? xs_bytes<T>() : (WIN * 4 + 15) / 16 * 16);
+    static constexpr int off_xch = 0;
+    static constexpr int off_stage = off_xch + FW * XCH_BYTES;
+    static constexpr int off_rows = off_stage + FW * PF_STAGE_BYTES;
+    static constexpr int off_win = off_rows + FW * AU_ROW * 4;
+    static constexpr int off_tw = off_win + (NLIVE_C * (int)sizeof(C) + 15) / 16 * 16;
+    static constexpr int off_wp = off_tw + 1024 * (int)sizeof(C);
+    static constexpr int off_w = off_wp + (WP_TABLE ? 1024 * (int)sizeof(C) : 0);
+    static constexpr int off_k0 = off_w + AU_MAX_ROUNDS * 64 * 16;
+    static constexpr int off_mel = off_k0 + AU_MAX_ROUNDS * 32 * 4;
+    static constexpr int bytes = off_mel + NMELS * 8;
+    static_assert(XCH_BYTES >= AU_MAX_ROUNDS * 32 * 4, "partial sums live in the idle exchange buffer");
+    static_assert(bytes <= 227 * 1024, "shared memory budget");
+};
+
+template <class T, int FW>
+__global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendParams P, const MelItems MI) {
+    using C = cplx_t<T>;
+    using L = FeAuLayout<T, FW>;
+    constexpr int NT = FW * 32;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    C* s_win = reinterpret_cast<C*>(smem + L::off_win);
+    C* s_tw = reinterpret_cast<C*>(smem + L::off_tw);
+    float4* s_w = reinterpret_cast<float4*>(smem + L::off_w);
+    int* s_k0 = reinterpret_cast<int*>(smem + L::off_k0);
+    int2* s_mel = reinterpret_cast<int2*>(smem + L::off_mel);
+    float* row = reinterpret_cast<float*>(smem + L::off_rows) + warp * AU_ROW;
+    T* xs = reinterpret_cast<T*>(smem + L::off_xch + warp * L::XCH_BYTES);
+    unsigned char* stage = smem + L::off_stage + warp * PF_STAGE_BYTES;
+
+    for (int i = tid; i < NLIVE_C; i += NT) s_win[i] = reinterpret_cast<const C*>(P.win2)[i];
+    for (int i = tid; i < 1024; i += NT) s_tw[i] = reinterpret_cast<const C*>(P.tw1024)[i];
+    if constexpr (L::WP_TABLE) {
+        C* s_wp = reinterpret_cast<C*>(smem + L::off_wp);
+        for (int i = tid; i < 1024; i += NT) s_wp[i] = reinterpret_cast<const C*>(P.wp2)[i];
+    }
+    const int rounds = MI.rounds;
+    for (int i = tid; i < rounds * 64; i += NT) s_w[i] = MI.w[i];
+    for (int i = tid; i < rounds * 32; i += NT) s_k0[i] = MI.k0[i];
+    for (int i = tid; i < NMELS; i += NT) s_mel[i] = MI.mel[i];
+    for (int i = tid; i < FW * AU_ROW; i += NT) reinterpret_cast<float*>(smem + L::off_rows)[i] = 0.0f;   // incl. the padding
+    __syncthreads();                                                      // the only CTA-wide barrier
+
+    auto wp = [&]() {
+        if constexpr (L::WP_TABLE) return WpTable<T>{reinterpret_cast<const C*>(smem + L::off_wp)};
+        else return WpLane<T>{reinterpret_cast<const C*>(P.wp2)[lane]};
+    }();
+
+    // this warp's run of frames: an equal share of all frames of the batch
+    const long long F = P.frame_off[P.B];
+    const long long NW = (long long)gridDim.x * FW, gw = (long long)blockIdx.x * FW + warp;
+    const int fa = (int)(F * gw / NW), fb = (int)(F * (gw + 1) / NW);
+    if (fa >= fb) return;
+    int b;
+    {   // last b with frame_off[b] <= fa
+        int lo = 0, hi = P.B;
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P.frame_off[mid] <= fa) lo = mid; else hi = mid; }
+        b = lo;
+    }
+    int fbase = 0, fend = 0, N = 0;
+    long long wbase = 0;
+    auto utt = [&](int bb) {
+        fbase = P.frame_off[bb];
+        fend = P.frame_off[bb + 1];
+        const int s0 = P.bounds[2 * bb];
+        N = P.bounds[2 * bb + 1] - s0;
+        wbase = P.wave_off[bb] + s0;
+    };
+    utt(b);
+    auto prefetched = [&](int t) { return P.wave_is_i16 && pf_interior(t, N); };
+    if (prefetched(fa - fbase)) pf_issue(P.wave, wbase, fa - fbase, stage, lane);
+
+    float* partial = reinterpret_cast<float*>(xs);                        // item sums: the exchange buffer is idle then
+#pragma unroll 1
+    for (int f = fa; f < fb; ++f) {
+        if (f >= fend) { do { ++b; } while (f >= P.frame_off[b + 1]); utt(b); }
+        const int t = f - fbase;
+        const int Tb = fend - fbase;
+        C v[32];
+        if (prefetched(t)) {
+            cp_async_wait_all();
+            __syncwarp();
+            const long long A = wbase + (HOP * t + WIN_LPAD - HALF) - 1;
+            const int s0 = (int)(A & 7);                                  // sample offset of A inside the first chunk
+            window_i16_words<T>(v, reinterpret_cast<const uint32_t*>(stage) + (s0 >> 1) + lane, (s0 & 1) != 0, s_win, lane);
+            __syncwarp();
+        } else if (P.wave_is_i16) {
+            load_frame<T, true>(v, P.wave, wbase, N, t, s_win, reinterpret_cast<float*>(xs), lane);
+        } else {
+            load_frame<T, false>(v, P.wave, wbase, N, t, s_win, reinterpret_cast<float*>(xs), lane);
+        }
+        // next frame of the same utterance: its samples land while this one is transformed (the first frames of an
+        // utterance are edge frames and never prefetched, so nothing is lost at a boundary)
+        if (f + 1 < fb && f + 1 < fend && prefetched(t + 1)) pf_issue(P.wave, wbase, t + 1, stage, lane);
+
+        warp_fft1024_split<T, 18>(v, xs, s_tw, lane);
+
+        float* mrow = P.mag_out ? P.mag_out + (size_t)f * NBINS : nullptr;
+        {
+            float pa[16], pb[16], p512 = 0.0f;
+            rfft_post_pairs<T>(v, reinterpret_cast<C*>(xs), wp, lane, [&](auto jj, C xa, C xb) {
+                constexpr int j = decltype(jj)::value;
+                const float ar = (float)xa.x, ai = (float)xa.y;          // complex64 storage of librosa.stft
+                const float br = (float)xb.x, bi = (float)xb.y;
+                pa[j] = fmaf(ar, ar, ai * ai);
+                pb[j] = fmaf(br, br, bi * bi);
+            }, [&](C x) { const float r = (float)x.x, i = (float)x.y; p512 = fmaf(r, r, i * i); });
+            float* rowa = row + lane;
+            float* rowb = row + 1024 - lane;
+            static_for<0, 16>([&](auto jj) {
+                constexpr int j = decltype(jj)::value;
+                rowa[32 * j] = sqrt_approx(pa[j]);                        // np.abs
+                rowb[-32 * j] = sqrt_approx(pb[j]);
+            });
+            if (lane == 0) row[512] = sqrt_approx(p512);
+            if (mrow) {
+                float* ma = mrow + lane;
+                float* mb = mrow + 1024 - lane;
+                static_for<0, 16>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    ma[32 * j] = db_norm_pw_nf(pa[j]);
+                    mb[-32 * j] = db_norm_pw_nf(pb[j]);
+                });
+                if (lane == 0) mrow[512] = db_norm_pw_nf(p512);
+            }
+        }
+        __syncwarp();                                                     // row complete; park buffer reads done
+
+        // ---- filterbank: items of 8 bins, then the mels in item order ----
+#pragma unroll 2
+        for (int r = 0; r < rounds; ++r) {
+            const float* x = row + s_k0[r * 32 + lane];
+            const float4 x0 = *reinterpret_cast<const float4*>(x), x1 = *reinterpret_cast<const float4*>(x + 4);
+            const float4 w0 = s_w[r * 64 + lane], w1 = s_w[r * 64 + 32 + lane];
+            float acc = x0.x * w0.x;
+            acc = fmaf(x0.y, w0.y, acc); acc = fmaf(x0.z, w0.z, acc); acc = fmaf(x0.w, w0.w, acc);
+            acc = fmaf(x1.x, w1.x, acc); acc = fmaf(x1.y, w1.y, acc); acc = fmaf(x1.z, w1.z, acc); acc = fmaf(x1.w, w1.w, acc);
+            partial[r * 32 + lane] = acc;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int m = lane; m < NMELS; m += 32) {
+            const int2 it = s_mel[m];
+            float s = partial[it.x];
+            for (int i = 1; i < it.y; ++i) s += partial[it.x + i];
+            const float val = db_norm(s);
+            if (P.mel_layout == 0) P.mel_out[(size_t)NMELS * fbase + (size_t)m * Tb + t] = val;
+            else P.mel_out[((size_t)b * P.T_max + t) * NMELS + m] = val;
+        }
+        __syncwarp();                                                     // partial sums read before xs is reused
+    }
+}
+
+}  // namespace unast

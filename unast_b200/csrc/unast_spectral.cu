@@ -12,6 +12,7 @@
 #include "frontend.cuh"
 #include "frontend_pf.cuh"
 #include "frontend_ws.cuh"
+#include "frontend_au.cuh"
 #include "griffinlim.cuh"
 #include "griffinlim_pk.cuh"
 #include "trim.cuh"
@@ -57,6 +58,10 @@ constexpr int FE_F32_THREADS = 16 * 32;
 // two-frames-per-warp cooperative kernel
 #ifndef UNAST_FE64_PF
 #define UNAST_FE64_PF 12
+#endif
+// UNAST_FE64_AU = number of warps of the warp-autonomous kernel (frontend_au.cuh); 0 = one of the tile kernels below
+#ifndef UNAST_FE64_AU
+#define UNAST_FE64_AU 12
 #endif
 // UNAST_FE64_WS = 1: the warp-specialised kernel (frontend_ws.cuh: 12 FFT warps + 4 mel warps)
 #ifndef UNAST_FE64_WS
@@ -154,6 +159,8 @@ struct unast_ctx {
     int pair_begin[11] = {0};
     MelUnit* units8 = nullptr; MelUnit* units16 = nullptr; MelUnit* unitsN = nullptr; MelUnit* units4 = nullptr;   // cooperative mel phase: unit lists for 8 / 16 warps
     MelCoop coop8, coop16, coopN, coop4;
+    MelItems items{};
+    float4* it_w = nullptr; int* it_k0 = nullptr; int2* it_mel = nullptr;
     int* d_err = nullptr;
     std::vector<float> mel_basis;
 };
@@ -421,17 +428,50 @@ int unast_create(int device, unast_ctx** out) {
     build_coop(UNAST_FE64_PF ? UNAST_FE64_PF : 8, h_unitsN, c->coopN);
     build_coop(WS_MW, h_units4, c->coop4);
 
+    // filterbank items of the warp-autonomous kernel (frontend_au.cuh): every mel's run of non-zero bins cut into
+    // pieces of 8 bins that start at a multiple of 4, dealt to (round, lane) slots in (mel, piece) order
+    std::vector<float4> it_w;
+    std::vector<int> it_k0;
+    std::vector<int2> it_mel(NMELS);
+    {
+        std::vector<std::pair<int, int>> items;                          // (mel, k0)
+        for (int m = 0; m < NMELS; ++m) {
+            int lo = -1, hi = -1;
+            for (int k = 0; k < NBINS; ++k) if (c->mel_basis[(size_t)m * NBINS + k] != 0.f) { if (lo < 0) lo = k; hi = k; }
+            it_mel[m] = make_int2((int)items.size(), 0);
+            if (lo < 0) { items.push_back({m, 0}); it_mel[m].y = 1; continue; }     // empty filter: one all-zero item
+            for (int k0 = lo & ~3; k0 <= hi; k0 += 8) { items.push_back({m, k0}); ++it_mel[m].y; }
+        }
+        const int rounds = ((int)items.size() + 31) / 32;
+        if (rounds > AU_MAX_ROUNDS) { delete c; return fail(UNAST_E_ARG, "unast_create: filterbank item plan exceeds AU_MAX_ROUNDS"); }
+        it_w.assign((size_t)rounds * 64, make_float4(0.f, 0.f, 0.f, 0.f));
+        it_k0.assign((size_t)rounds * 32, 0);
+        for (size_t i = 0; i < items.size(); ++i) {
+            const int r = (int)(i / 32), l = (int)(i % 32), m = items[i].first, k0 = items[i].second;
+            auto wt = [&](int k) { return k < NBINS ? c->mel_basis[(size_t)m * NBINS + k] : 0.f; };
+            it_k0[i] = k0;
+            it_w[(size_t)r * 64 + l] = make_float4(wt(k0), wt(k0 + 1), wt(k0 + 2), wt(k0 + 3));
+            it_w[(size_t)r * 64 + 32 + l] = make_float4(wt(k0 + 4), wt(k0 + 5), wt(k0 + 6), wt(k0 + 7));
+        }
+        c->items.rounds = rounds;
+    }
+
     cudaError_t e = cudaSuccess;
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
     up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
     up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
     up(&c->tw4_f, tw4_f); up(&c->tw4a_f, tw4a_f); up(&c->wp4_f, wp4_f); up(&c->units8, h_units8); up(&c->units16, h_units16); up(&c->unitsN, h_unitsN); up(&c->units4, h_units4);
     up(&c->wa2_f, wa2_f); up(&c->rinv_l, rinv_l); up(&c->rinv_r, rinv_r);
+    up(&c->it_w, it_w); up(&c->it_k0, it_k0); up(&c->it_mel, it_mel);
     up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F32_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF32::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F64_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF64::bytes);
+#if UNAST_FE64_AU
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, UNAST_FE64_AU>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, UNAST_FE64_AU>::bytes);
+#endif
+    c->items.w = c->it_w; c->items.k0 = c->it_k0; c->items.mel = c->it_mel;
     if (e == cudaSuccess) e = cudaFuncSetAttribute(GL_KERNEL<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GL_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(GL_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GL_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
@@ -448,6 +488,7 @@ int unast_destroy(unast_ctx* c) {
     cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
     cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f); cudaFree(c->units8); cudaFree(c->units16); cudaFree(c->unitsN); cudaFree(c->units4);
     cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
+    cudaFree(c->it_w); cudaFree(c->it_k0); cudaFree(c->it_mel);
     cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
     delete c;
     return UNAST_OK;
@@ -537,7 +578,9 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
     } else {
         step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF64::R, tile_off);
         P.win2 = i16 ? (const void*)c->win2i_d : (const void*)c->win2_d; P.tw1024 = c->tw_d; P.wp2 = c->wp_d;
-#if UNAST_FE_SPECIALISED
+#if UNAST_FE64_AU
+        frontend_au_kernel<double, UNAST_FE64_AU><<<c->num_sms, UNAST_FE64_AU * 32, FeAuLayout<double, UNAST_FE64_AU>::bytes, st>>>(P, c->items);
+#elif UNAST_FE_SPECIALISED
         FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P);
 #else
         FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P, c->FE_F64_COOP);

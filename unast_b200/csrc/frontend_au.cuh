@@ -19,13 +19,14 @@
 namespace unast {
 
 constexpr int AU_ROW = 1032;                 // floats per |X| row: bins 0..1024 + zero padding up to the last item's end
-constexpr int AU_MAX_ROUNDS = 12;
+constexpr int AU_BATCH = 5;                  // rounds per batch; the host pads the tables to a multiple of it
+constexpr int AU_MAX_ROUNDS = 15;
 
 struct MelItems {                            // device arrays, built once on the host (unast_spectral.cu)
     const float4* w;                         // [rounds][2][32]: weights of bins k0..k0+3 / k0+4..k0+7 of slot (round, lane)
     const int* k0;                           // [rounds][32]: first bin of the slot's item (multiple of 4); idle slots: 0, weights 0
     const int2* mel;                         // [80]: (first item id = round * 32 + lane, number of items)
-    int rounds;
+    int rounds;                              // multiple of AU_BATCH (padding slots: k0 = 0, weights 0)
 };
 
 template <class T, int FW>
@@ -162,22 +163,37 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
         __syncwarp();                                                     // row complete; park buffer reads done
 
         // ---- filterbank: items of 8 bins, then the mels in item order ----
-#pragma unroll 2
-        for (int r = 0; r < rounds; ++r) {
-            const float* x = row + s_k0[r * 32 + lane];
-            const float4 x0 = *reinterpret_cast<const float4*>(x), x1 = *reinterpret_cast<const float4*>(x + 4);
-            const float4 w0 = s_w[r * 64 + lane], w1 = s_w[r * 64 + 32 + lane];
-            float acc = x0.x * w0.x;
-            acc = fmaf(x0.y, w0.y, acc); acc = fmaf(x0.z, w0.z, acc); acc = fmaf(x0.w, w0.w, acc);
-            acc = fmaf(x1.x, w1.x, acc); acc = fmaf(x1.y, w1.y, acc); acc = fmaf(x1.z, w1.z, acc); acc = fmaf(x1.w, w1.w, acc);
-            partial[r * 32 + lane] = acc;
+        // batches of AU_BATCH rounds: all addresses, then all 128-bit loads, then two FMA chains per item -- the
+        // shared-memory latency of one batch is paid once, not once per item
+#pragma unroll 1
+        for (int r0 = 0; r0 < rounds; r0 += AU_BATCH) {
+            int k0[AU_BATCH];
+#pragma unroll
+            for (int i = 0; i < AU_BATCH; ++i) k0[i] = s_k0[(r0 + i) * 32 + lane];
+            float4 x0[AU_BATCH], x1[AU_BATCH], w0[AU_BATCH], w1[AU_BATCH];
+#pragma unroll
+            for (int i = 0; i < AU_BATCH; ++i) {
+                x0[i] = *reinterpret_cast<const float4*>(row + k0[i]);
+                x1[i] = *reinterpret_cast<const float4*>(row + k0[i] + 4);
+                w0[i] = s_w[(r0 + i) * 64 + lane];
+                w1[i] = s_w[(r0 + i) * 64 + 32 + lane];
+            }
+#pragma unroll
+            for (int i = 0; i < AU_BATCH; ++i) {
+                float a = x0[i].x * w0[i].x, c = x1[i].x * w1[i].x;
+                a = fmaf(x0[i].y, w0[i].y, a); c = fmaf(x1[i].y, w1[i].y, c);
+                a = fmaf(x0[i].z, w0[i].z, a); c = fmaf(x1[i].z, w1[i].z, c);
+                a = fmaf(x0[i].w, w0[i].w, a); c = fmaf(x1[i].w, w1[i].w, c);
+                partial[(r0 + i) * 32 + lane] = a + c;
+            }
         }
         __syncwarp();
 #pragma unroll
         for (int m = lane; m < NMELS; m += 32) {
             const int2 it = s_mel[m];
+            const int nmax = __reduce_max_sync(__activemask(), it.y);     // warp-uniform trip count, predicated adds
             float s = partial[it.x];
-            for (int i = 1; i < it.y; ++i) s += partial[it.x + i];
+            for (int i = 1; i < nmax; ++i) { const float q = partial[it.x + min(i, it.y - 1)]; s += i < it.y ? q : 0.0f; }
             const float val = db_norm(s);
             if (P.mel_layout == 0) P.mel_out[(size_t)NMELS * fbase + (size_t)m * Tb + t] = val;
             else P.mel_out[((size_t)b * P.T_max + t) * NMELS + m] = val;

@@ -43,7 +43,8 @@ struct FeAuLayout {
     static constexpr int off_w = off_wp + (WP_TABLE ? 1024 * (int)sizeof(C) : 0);
     static constexpr int off_k0 = off_w + AU_MAX_ROUNDS * 64 * 16;
     static constexpr int off_mel = off_k0 + AU_MAX_ROUNDS * 32 * 4;
-    static constexpr int bytes = off_mel + NMELS * 8;
+    static constexpr int off_state = off_mel + NMELS * 8;                // per-warp loop state, 8 words each
+    static constexpr int bytes = off_state + FW * 32;
     static_assert(XCH_BYTES >= AU_MAX_ROUNDS * 32 * 4, "partial sums live in the idle exchange buffer");
     static_assert(bytes <= 227 * 1024, "shared memory budget");
 };
@@ -93,45 +94,63 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
         while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P.frame_off[mid] <= fa) lo = mid; else hi = mid; }
         b = lo;
     }
-    int fbase = 0, fend = 0, N = 0;
-    long long wbase = 0;
-    auto utt = [&](int bb) {
-        fbase = P.frame_off[bb];
-        fend = P.frame_off[bb + 1];
+    // Loop state lives in shared memory, re-read (volatile) where it is needed: next to 128 registers of frame data the
+    // register allocator would spill it to local memory, and every reload then stalls on the long scoreboard
+    // (profiles/r2c_ncu_fe_f64.txt: ~9 % of the samples sat on such reloads).
+    //   st[0] f, st[1] fb, st[2] fend, st[3] fbase, st[4] N, st[5] b, st[6..7] wbase
+    volatile int* st = reinterpret_cast<volatile int*>(smem + L::off_state) + warp * 8;
+    auto utt = [&](int bb) {                                              // lane 0 only
+        st[3] = P.frame_off[bb];
+        st[2] = P.frame_off[bb + 1];
         const int s0 = P.bounds[2 * bb];
-        N = P.bounds[2 * bb + 1] - s0;
-        wbase = P.wave_off[bb] + s0;
+        st[4] = P.bounds[2 * bb + 1] - s0;
+        st[5] = bb;
+        *reinterpret_cast<volatile long long*>(st + 6) = P.wave_off[bb] + s0;
     };
-    utt(b);
-    auto prefetched = [&](int t) { return P.wave_is_i16 && pf_interior(t, N); };
-    if (prefetched(fa - fbase)) pf_issue(P.wave, wbase, fa - fbase, stage, lane);
+    if (lane == 0) { st[0] = fa; st[1] = fb; utt(b); }
+    __syncwarp();
+    auto wbase_of = [&]() { return *reinterpret_cast<volatile long long*>(st + 6); };
+    auto prefetched = [&](int t) { return P.wave_is_i16 && pf_interior(t, st[4]); };
+    if (prefetched(fa - st[3])) pf_issue(P.wave, wbase_of(), fa - st[3], stage, lane);
 
     float* partial = reinterpret_cast<float*>(xs);                        // item sums: the exchange buffer is idle then
 #pragma unroll 1
-    for (int f = fa; f < fb; ++f) {
-        if (f >= fend) { do { ++b; } while (f >= P.frame_off[b + 1]); utt(b); }
-        const int t = f - fbase;
-        const int Tb = fend - fbase;
-        C v[32];
-        if (prefetched(t)) {
-            cp_async_wait_all();
-            __syncwarp();
-            const long long A = wbase + (HOP * t + WIN_LPAD - HALF) - 1;
-            const int s0 = (int)(A & 7);                                  // sample offset of A inside the first chunk
-            window_i16_words<T>(v, reinterpret_cast<const uint32_t*>(stage) + (s0 >> 1) + lane, (s0 & 1) != 0, s_win, lane);
-            __syncwarp();
-        } else if (P.wave_is_i16) {
-            load_frame<T, true>(v, P.wave, wbase, N, t, s_win, reinterpret_cast<float*>(xs), lane);
-        } else {
-            load_frame<T, false>(v, P.wave, wbase, N, t, s_win, reinterpret_cast<float*>(xs), lane);
+    for (;;) {
+        {
+            const int f = st[0];
+            if (f >= st[1]) break;
+            if (f >= st[2]) {                                             // the run crosses into the next utterance
+                __syncwarp();
+                if (lane == 0) { int bb = st[5]; do { ++bb; } while (f >= P.frame_off[bb + 1]); utt(bb); }
+                __syncwarp();
+            }
         }
-        // next frame of the same utterance: its samples land while this one is transformed (the first frames of an
-        // utterance are edge frames and never prefetched, so nothing is lost at a boundary)
-        if (f + 1 < fb && f + 1 < fend && prefetched(t + 1)) pf_issue(P.wave, wbase, t + 1, stage, lane);
+        C v[32];
+        {
+            const int t = st[0] - st[3];
+            const int N = st[4];
+            const long long wbase = wbase_of();
+            if (prefetched(t)) {
+                cp_async_wait_all();
+                __syncwarp();
+                const long long A = wbase + (HOP * t + WIN_LPAD - HALF) - 1;
+                const int s0 = (int)(A & 7);                              // sample offset of A inside the first chunk
+                window_i16_words<T>(v, reinterpret_cast<const uint32_t*>(stage) + (s0 >> 1) + lane, (s0 & 1) != 0, s_win, lane);
+                __syncwarp();
+            } else if (P.wave_is_i16) {
+                load_frame<T, true>(v, P.wave, wbase, N, t, s_win, reinterpret_cast<float*>(xs), lane);
+            } else {
+                load_frame<T, false>(v, P.wave, wbase, N, t, s_win, reinterpret_cast<float*>(xs), lane);
+            }
+            // next frame of the same utterance: its samples land while this one is transformed (the first frames of
+            // an utterance are edge frames and never prefetched, so nothing is lost at a boundary)
+            const int f1 = st[0] + 1;
+            if (f1 < st[1] && f1 < st[2] && prefetched(t + 1)) pf_issue(P.wave, wbase, t + 1, stage, lane);
+        }
 
         warp_fft1024_split<T, 18>(v, xs, s_tw, lane);
 
-        float* mrow = P.mag_out ? P.mag_out + (size_t)f * NBINS : nullptr;
+        float* mrow = P.mag_out ? P.mag_out + (size_t)st[0] * NBINS : nullptr;
         {
             float pa[16], pb[16], p512 = 0.0f;
             rfft_post_pairs<T>(v, reinterpret_cast<C*>(xs), wp, lane, [&](auto jj, C xa, C xb) {
@@ -195,10 +214,13 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
             float s = partial[it.x];
             for (int i = 1; i < nmax; ++i) { const float q = partial[it.x + min(i, it.y - 1)]; s += i < it.y ? q : 0.0f; }
             const float val = db_norm(s);
-            if (P.mel_layout == 0) P.mel_out[(size_t)NMELS * fbase + (size_t)m * Tb + t] = val;
-            else P.mel_out[((size_t)b * P.T_max + t) * NMELS + m] = val;
+            const int fbase = st[3], t = st[0] - fbase;
+            if (P.mel_layout == 0) P.mel_out[(size_t)NMELS * fbase + (size_t)m * (st[2] - fbase) + t] = val;
+            else P.mel_out[((size_t)st[5] * P.T_max + t) * NMELS + m] = val;
         }
         __syncwarp();                                                     // partial sums read before xs is reused
+        if (lane == 0) st[0] = st[0] + 1;
+        __syncwarp();
     }
 }
 

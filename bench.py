@@ -328,7 +328,7 @@ def run_ours(args):
     achieved = my_frames * bytes_per_frame / (fe_kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "traffic": ncu_traffic(args.precision, my_frames),
-                "kernel": "frontend_au_kernel<double,12>" if args.precision == "f64" else "frontend_coop_kernel<float,16,1>",
+                "kernel": "frontend_au_kernel<double,12>" if args.precision == "f64" else "frontend_au_kernel<float,16>",
                 "kernel_ms": fe_kernel_ms, "frames_per_launch": my_frames, "bytes_per_frame": bytes_per_frame,
                 "peak_source": peak_src,
                 "fft_tflops": my_frames * FFT_FLOP / (fe_kernel_ms * 1e-3) / 1e12}

@@ -63,6 +63,10 @@ constexpr int FE_F32_THREADS = 16 * 32;
 #ifndef UNAST_FE64_AU
 #define UNAST_FE64_AU 12
 #endif
+// UNAST_FE32_AU = number of warps of the same kernel in float32 mode; 0 = the float32 tile kernel
+#ifndef UNAST_FE32_AU
+#define UNAST_FE32_AU 16
+#endif
 // UNAST_FE64_WS = 1: the warp-specialised kernel (frontend_ws.cuh: 12 FFT warps + 4 mel warps)
 #ifndef UNAST_FE64_WS
 #define UNAST_FE64_WS 0
@@ -468,6 +472,9 @@ int unast_create(int device, unast_ctx** out) {
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F32_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF32::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F64_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF64::bytes);
+#if UNAST_FE32_AU
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<float, UNAST_FE32_AU>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<float, UNAST_FE32_AU>::bytes);
+#endif
 #if UNAST_FE64_AU
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, UNAST_FE64_AU>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, UNAST_FE64_AU>::bytes);
 #endif
@@ -570,7 +577,9 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
     if (precision == UNAST_PREC_F32) {
         step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF32::R, tile_off);
         P.win2 = i16 ? c->win2i_f : c->win2_f; P.tw1024 = c->tw_f; P.wp2 = c->wp_f;
-#if UNAST_FE_SPECIALISED
+#if UNAST_FE32_AU
+        frontend_au_kernel<float, UNAST_FE32_AU><<<c->num_sms, UNAST_FE32_AU * 32, FeAuLayout<float, UNAST_FE32_AU>::bytes, st>>>(P, c->items);
+#elif UNAST_FE_SPECIALISED
         FE_F32_KERNEL<<<c->num_sms, FE_F32_THREADS, FeF32::bytes, st>>>(P);
 #else
         FE_F32_KERNEL<<<c->num_sms, FE_F32_THREADS, FeF32::bytes, st>>>(P, c->coop16);

@@ -74,92 +74,7 @@ __device__ __forceinline__ double2 cmul(double2 a, double2 w) {
 __device__ __forceinline__ float fma_t(float a, float b, float c) { return fmaf(a, b, c); }
 __device__ __forceinline__ double fma_t(double a, double b, double c) { return fma(a, b, c); }
 
-// ---- mbarrier (shared-memory transaction barrier) helpers: producer/consumer hand-off between warps --------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(smem_u32(bar)), "r"(parity)
-            : "memory");
-    } while (!done);
-}
-
-// the same wait as one opaque statement (the retry loop lives inside the PTX block): no loop in the compiler's control
-// flow graph, so a wait in the middle of a register-heavy section does not perturb register allocation
-__device__ __forceinline__ void mbar_wait_inline(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred P1;\n\t"
-        "LAB_WAIT:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-        "@P1 bra DONE;\n\t"
-        "bra LAB_WAIT;\n\t"
-        "DONE:\n\t}"
-        ::"r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-}
-
-// ---- tensor memory (TMEM) as a per-SM operand store ----------------------------------------------------
-// 512 columns x 128 lanes x 32 bit per SM.  A warp reaches the 32 lanes of its own quadrant (warp id % 4) with the
-// 32x32b shape: thread i <-> lane 32 (warp % 4) + i, consecutive registers <-> consecutive columns.
-// Address: bits 31..16 lane, 15..0 column.
-__device__ __forceinline__ void tmem_alloc(uint32_t* smem_result, int ncols /* power of two, 32..512 */) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)), "r"(ncols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, int ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tmem_fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tmem_fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tmem_st4(uint32_t taddr, float4 v) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(__float_as_uint(v.x)),
-                 "r"(__float_as_uint(v.y)), "r"(__float_as_uint(v.z)), "r"(__float_as_uint(v.w))
-                 : "memory");
-}
-__device__ __forceinline__ void tmem_st2(uint32_t taddr, float2 v) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(__float_as_uint(v.x)), "r"(__float_as_uint(v.y)) : "memory");
-}
-__device__ __forceinline__ float2 tmem_ld2(uint32_t taddr) {
-    uint32_t a, b;
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(taddr) : "memory");
-    return make_float2(__uint_as_float(a), __uint_as_float(b));
-}
-__device__ __forceinline__ void tmem_wait_ld(float2& v, float2& w) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+f"(v.x), "+f"(v.y), "+f"(w.x), "+f"(w.y)::"memory");
-}
-__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ float4 tmem_ld4(uint32_t taddr) {
-    uint32_t a, b, c, d;
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(taddr) : "memory");
-    return make_float4(__uint_as_float(a), __uint_as_float(b), __uint_as_float(c), __uint_as_float(d));
-}
-// The loaded registers may only be read after the wait: the "+f" operands tie them to it so the compiler cannot
-// hoist a use above the wait.
-__device__ __forceinline__ void tmem_wait_ld(float4& v) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w)::"memory");
-}
-__device__ __forceinline__ void tmem_wait_ld(float4& v, float4& w) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;"
-                 : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w), "+f"(w.x), "+f"(w.y), "+f"(w.z), "+f"(w.w)::"memory");
-}
-
-__device__ __forceinline__ void tmem_wait_ld(float4& a, float4& b, float4& c, float4& d) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;"
-                 : "+f"(a.x), "+f"(a.y), "+f"(a.z), "+f"(a.w), "+f"(b.x), "+f"(b.y), "+f"(b.z), "+f"(b.w),
-                   "+f"(c.x), "+f"(c.y), "+f"(c.z), "+f"(c.w), "+f"(d.x), "+f"(d.y), "+f"(d.z), "+f"(d.w)::"memory");
-}
 
 // ---- cp.async (LDGSTS) helpers: 16-byte global -> shared copies that bypass registers ------------------
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {

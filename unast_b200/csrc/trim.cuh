@@ -147,36 +147,6 @@ __global__ void __launch_bounds__(1024) frame_offsets_kernel(const int* __restri
     }
 }
 
-// step_off[b] = prefix sum of ceil(T_b / fps); single CTA (same scan, different summand).
-__global__ void __launch_bounds__(1024) step_offsets_kernel(const int* __restrict__ frame_off, int B, int fps,
-                                                            int* __restrict__ step_off) {
-    __shared__ int s_warp[32];
-    __shared__ int s_total;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { s_total = 0; step_off[0] = 0; }
-    __syncthreads();
-    for (int base = 0; base < B; base += 1024) {
-        const int b = base + tid;
-        int x = b < B ? (frame_off[b + 1] - frame_off[b] + fps - 1) / fps : 0;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
-        if (lane == 31) s_warp[warp] = x;
-        __syncthreads();
-        if (warp == 0) {
-            int w = s_warp[lane];
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { int y = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += y; }
-            s_warp[lane] = w;
-        }
-        __syncthreads();
-        const int incl = x + (warp ? s_warp[warp - 1] : 0) + s_total;
-        if (b < B) step_off[b + 1] = incl;
-        __syncthreads();
-        if (tid == 1023) s_total = incl;
-        __syncthreads();
-    }
-}
-
 // K2: S = (10^((clip(m,0,1)*max_db - max_db + ref_db) * 0.05))^power, float32 (utils.py:289-298).
 // power == 0 passes `mag` through unchanged (griffin_lim / invert_spectrogram called on a linear spectrogram).
 __global__ void gl_prepare_kernel(const float* __restrict__ mag, long long total_frames, float power, float* __restrict__ S) {

@@ -9,85 +9,16 @@
 #include <vector>
 
 #include "../../include/unast_spectral.h"
-#include "frontend.cuh"
-#include "frontend_pf.cuh"
-#include "frontend_ws.cuh"
 #include "frontend_au.cuh"
-#include "griffinlim.cuh"
 #include "griffinlim_pk.cuh"
 #include "trim.cuh"
 #include "augment.cuh"
 
 using namespace unast;
 
-// Griffin-Lim iteration kernel: 1 = packed f32x2 FFT core (griffinlim_pk.cuh), 0 = scalar (griffinlim.cuh)
-#ifndef UNAST_GL_PK
-#define UNAST_GL_PK 1
-#endif
-#if UNAST_GL_PK
-#define GL_KERNEL gl_pk_kernel
-#define GL_SMEM glp_smem_bytes
-#else
-#define GL_KERNEL gl_kernel
-#define GL_SMEM gl_smem_bytes
-#endif
-
-// Front-end kernel configurations.  Default: the cooperative kernel (every warp an FFT warp, mel phase shared by all
-// warps); -DUNAST_FE_SPECIALISED=1 selects the warp-specialised variant (dedicated mel warps) for A/B runs.
-#ifndef UNAST_FE_SPECIALISED
-#define UNAST_FE_SPECIALISED 0
-#endif
-#ifndef UNAST_FE64_FW
-#define UNAST_FE64_FW 7
-#endif
-#ifndef UNAST_FE64_RPW
-#define UNAST_FE64_RPW 2
-#endif
-#if UNAST_FE_SPECIALISED
-using FeF32 = FeLayout<float, 14, 1, 2>;
-using FeF64 = FeLayout<double, UNAST_FE64_FW, UNAST_FE64_RPW, 1>;
-#define FE_F32_KERNEL frontend_kernel<float, 14, 1, 2>
-#define FE_F64_KERNEL frontend_kernel<double, UNAST_FE64_FW, UNAST_FE64_RPW, 1>
-constexpr int FE_F32_THREADS = (14 + 2) * 32;
-constexpr int FE_F64_THREADS = (UNAST_FE64_FW + 1) * 32;
-#else
-using FeF32 = FeCoopLayout<float, 16, 1>;
-#define FE_F32_KERNEL frontend_coop_kernel<float, 16, 1>
-constexpr int FE_F32_THREADS = 16 * 32;
-// float64: UNAST_FE64_PF = number of warps of the prefetching split-exchange kernel (frontend_pf.cuh); 0 = the
-// two-frames-per-warp cooperative kernel
-#ifndef UNAST_FE64_PF
-#define UNAST_FE64_PF 12
-#endif
-// UNAST_FE64_AU = number of warps of the warp-autonomous kernel (frontend_au.cuh); 0 = one of the tile kernels below
-#ifndef UNAST_FE64_AU
-#define UNAST_FE64_AU 12
-#endif
-// UNAST_FE32_AU = number of warps of the same kernel in float32 mode; 0 = the float32 tile kernel
-#ifndef UNAST_FE32_AU
-#define UNAST_FE32_AU 16
-#endif
-// UNAST_FE64_WS = 1: the warp-specialised kernel (frontend_ws.cuh: 12 FFT warps + 4 mel warps)
-#ifndef UNAST_FE64_WS
-#define UNAST_FE64_WS 0
-#endif
-#if UNAST_FE64_WS
-using FeF64 = FeWsLayout<double>;
-#define FE_F64_KERNEL frontend_ws_kernel<double>
-constexpr int FE_F64_THREADS = (WS_FW + WS_MW) * 32;
-#define FE_F64_COOP coop4
-#elif UNAST_FE64_PF
-using FeF64 = FePfLayout<double, UNAST_FE64_PF>;
-#define FE_F64_KERNEL frontend_pf_kernel<double, UNAST_FE64_PF>
-constexpr int FE_F64_THREADS = UNAST_FE64_PF * 32;
-#define FE_F64_COOP coopN
-#else
-using FeF64 = FeCoopLayout<double, 8, 2>;
-#define FE_F64_KERNEL frontend_coop_kernel<double, 8, 2>
-constexpr int FE_F64_THREADS = 8 * 32;
-#define FE_F64_COOP coop8
-#endif
-#endif
+// warps per CTA of the fused front end (frontend_au.cuh): 12 x 168 registers in float64, 16 x 128 in float32
+constexpr int FE64_WARPS = 12;
+constexpr int FE32_WARPS = 16;
 
 namespace {
 
@@ -108,6 +39,20 @@ int fail(int code, const std::string& msg) {
 constexpr double kPi = 3.14159265358979323846264338327950288;
 
 size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+// Every launching entry point runs on the context's device whatever the caller's current device is, and leaves the
+// caller's current device as it found it.
+struct DeviceGuard {
+    int prev = -1;
+    bool good = true;
+    explicit DeviceGuard(int dev) {
+        int cur = -1;
+        good = cudaGetDevice(&cur) == cudaSuccess;
+        if (good && cur != dev) { good = cudaSetDevice(dev) == cudaSuccess; if (good) prev = cur; }
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    bool ok() const { return good; }
+};
 
 // ---- librosa.filters.mel(22050, 2048, 80): Slaney scale, area-normalised, float32 ----
 double hz_to_mel(double f) {
@@ -158,11 +103,6 @@ struct unast_ctx {
     float *wss_per = nullptr, *rinv_l = nullptr, *rinv_r = nullptr;
     float2* wa2_f = nullptr;
     double* w2 = nullptr;
-    float2* bfrag = nullptr;
-    int* pair_kb = nullptr;
-    int pair_begin[11] = {0};
-    MelUnit* units8 = nullptr; MelUnit* units16 = nullptr; MelUnit* unitsN = nullptr; MelUnit* units4 = nullptr;   // cooperative mel phase: unit lists for 8 / 16 warps
-    MelCoop coop8, coop16, coopN, coop4;
     MelItems items{};
     float4* it_w = nullptr; int* it_k0 = nullptr; int2* it_mel = nullptr;
     int* d_err = nullptr;
@@ -283,7 +223,8 @@ int unast_create(int device, unast_ctx** out) {
     int ndev = 0;
     CU(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(UNAST_E_ARG, "unast_create: no such CUDA device (there is no CPU fallback)");
-    CU(cudaSetDevice(device));
+    DeviceGuard guard(device);                                      // the caller's current device is restored on return
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "unast_create: cannot select the device");
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10) return fail(UNAST_E_ARG, "unast_create: built for sm_100a (Blackwell B200) only");
@@ -370,68 +311,6 @@ int unast_create(int device, unast_ctx** out) {
     c->mel_basis = build_mel_basis();
     for (int m = 0; m < NMELS; ++m)
         if (c->mel_basis[(size_t)m * NBINS + 1024] != 0.f) { delete c; return fail(UNAST_E_ARG, "filterbank has weight on the Nyquist bin"); }
-    std::vector<float2> bfrag;
-    std::vector<int> pair_kb;
-    for (int nt = 0; nt < NMELS / 8; ++nt) {
-        c->pair_begin[nt] = (int)pair_kb.size();
-        for (int kb = 0; kb < 128; ++kb) {
-            bool any = false;
-            for (int g = 0; g < 8 && !any; ++g)
-                for (int t = 0; t < 8; ++t)
-                    if (c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t] != 0.f) { any = true; break; }
-            if (!any) continue;
-            pair_kb.push_back(kb);
-            for (int lane = 0; lane < 32; ++lane) {
-                const int g = lane >> 2, t = lane & 3;
-                const float b0 = c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t];
-                const float b1 = c->mel_basis[(size_t)(8 * nt + g) * NBINS + 8 * kb + t + 4];
-                bfrag.push_back(make_float2(b0, b1));
-            }
-        }
-    }
-    c->pair_begin[NMELS / 8] = (int)pair_kb.size();
-    // Cooperative mel phase: n-tiles (split in two halves when clearly above the per-warp share) dealt to the warps
-    // longest-first; a warp's units are stored contiguously in the order it visits them.
-    std::vector<MelUnit> h_units8, h_units16, h_unitsN, h_units4;
-    auto build_coop = [&](int FW, std::vector<MelUnit>& out, MelCoop& mc) {
-        const int total = c->pair_begin[NMELS / 8];
-        const double share = (double)total / FW;
-        std::vector<MelUnit> items;
-        mc.nsplit = 0;
-        std::vector<int> order(NMELS / 8);
-        for (int nt = 0; nt < NMELS / 8; ++nt) order[nt] = nt;
-        std::sort(order.begin(), order.end(), [&](int a, int b) {
-            return (c->pair_begin[a + 1] - c->pair_begin[a]) > (c->pair_begin[b + 1] - c->pair_begin[b]); });
-        for (int nt : order) {                                         // largest first: they get the (at most 4) splits
-            const int p0 = c->pair_begin[nt], p1 = c->pair_begin[nt + 1], n = p1 - p0;
-            if (n > 1.15 * share && mc.nsplit < 4) {
-                const int mid = p0 + (n + 1) / 2;
-                items.push_back({nt, p0, mid, mc.nsplit});
-                items.push_back({nt, mid, p1, mc.nsplit});
-                mc.split_nt[mc.nsplit++] = nt;
-            } else {
-                items.push_back({nt, p0, p1, -1});
-            }
-        }
-        std::sort(items.begin(), items.end(), [](const MelUnit& a, const MelUnit& b) { return (a.p1 - a.p0) > (b.p1 - b.p0); });
-        std::vector<std::vector<MelUnit>> per(FW);
-        std::vector<int> load(FW, 0);
-        for (const MelUnit& it : items) {
-            int w = 0;
-            for (int k = 1; k < FW; ++k) if (load[k] < load[w]) w = k;
-            per[w].push_back(it);
-            load[w] += it.p1 - it.p0;
-        }
-        out.clear();
-        for (int w = 0; w < FW; ++w) { mc.unit_begin[w] = (int)out.size(); for (const MelUnit& it : per[w]) out.push_back(it); }
-        for (int w = FW; w <= 16; ++w) mc.unit_begin[w] = (int)out.size();
-        for (int k = mc.nsplit; k < 4; ++k) mc.split_nt[k] = 0;
-    };
-    build_coop(8, h_units8, c->coop8);
-    build_coop(16, h_units16, c->coop16);
-    build_coop(UNAST_FE64_PF ? UNAST_FE64_PF : 8, h_unitsN, c->coopN);
-    build_coop(WS_MW, h_units4, c->coop4);
-
     // filterbank items of the warp-autonomous kernel (frontend_au.cuh): every mel's run of non-zero bins cut into
     // pieces of 8 bins that start at a multiple of 4, dealt to (round, lane) slots in (mel, piece) order
     std::vector<float4> it_w;
@@ -464,49 +343,42 @@ int unast_create(int device, unast_ctx** out) {
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
     up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
     up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
-    up(&c->tw4_f, tw4_f); up(&c->tw4a_f, tw4a_f); up(&c->wp4_f, wp4_f); up(&c->units8, h_units8); up(&c->units16, h_units16); up(&c->unitsN, h_unitsN); up(&c->units4, h_units4);
+    up(&c->tw4_f, tw4_f); up(&c->tw4a_f, tw4a_f); up(&c->wp4_f, wp4_f);
     up(&c->wa2_f, wa2_f); up(&c->rinv_l, rinv_l); up(&c->rinv_r, rinv_r);
     up(&c->it_w, it_w); up(&c->it_k0, it_k0); up(&c->it_mel, it_mel);
-    up(&c->wss_per, wss_per); up(&c->w2, w2); up(&c->bfrag, bfrag); up(&c->pair_kb, pair_kb);
+    up(&c->wss_per, wss_per); up(&c->w2, w2);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F32_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF32::bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(FE_F64_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FeF64::bytes);
-#if UNAST_FE32_AU
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<float, UNAST_FE32_AU>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<float, UNAST_FE32_AU>::bytes);
-#endif
-#if UNAST_FE64_AU
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, UNAST_FE64_AU>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, UNAST_FE64_AU>::bytes);
-#endif
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<float, FE32_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<float, FE32_WARPS>::bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, FE64_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, FE64_WARPS>::bytes);
     c->items.w = c->it_w; c->items.k0 = c->it_k0; c->items.mel = c->it_mel;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(GL_KERNEL<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GL_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(GL_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GL_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_pk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_pk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
-    c->coop8.units = c->units8; c->coop16.units = c->units16; c->coopN.units = c->unitsN; c->coop4.units = c->units4;
-    if ((int)h_units8.size() > MEL_MAX_UNITS || (int)h_units16.size() > MEL_MAX_UNITS || (int)h_unitsN.size() > MEL_MAX_UNITS) { unast_destroy(c); return fail(UNAST_E_ARG, "unast_create: mel unit table too large"); }
     *out = c;
     return UNAST_OK;
 }
 
 int unast_destroy(unast_ctx* c) {
     if (!c) return UNAST_OK;
+    DeviceGuard guard(c->device);
     cudaFree(c->win2_f); cudaFree(c->win2i_f); cudaFree(c->win2i_d); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
     cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
-    cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f); cudaFree(c->units8); cudaFree(c->units16); cudaFree(c->unitsN); cudaFree(c->units4);
+    cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f);
     cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
     cudaFree(c->it_w); cudaFree(c->it_k0); cudaFree(c->it_mel);
-    cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->bfrag); cudaFree(c->pair_kb); cudaFree(c->d_err);
+    cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->d_err);
     delete c;
     return UNAST_OK;
 }
-
-static int npairs_of(const unast_ctx* c) { return c->pair_begin[NMELS / 8]; }
 
 int unast_num_sms(const unast_ctx* c) { return c ? c->num_sms : 0; }
 
 int unast_check(unast_ctx* c, void* stream) {
     if (!c) return fail(UNAST_E_ARG, "unast_check: ctx is NULL");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     int h = 0;
     CU(cudaMemcpyAsync(&h, c->d_err, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     CU(cudaStreamSynchronize((cudaStream_t)stream));
@@ -535,6 +407,8 @@ int unast_trim_bounds(unast_ctx* c, const void* wave, int dtype, const int64_t* 
     if (!c || !wave || !wave_off || !bounds_out || B <= 0 || max_len <= 0) return fail(UNAST_E_ARG, "unast_trim_bounds: bad argument");
     if (dtype != UNAST_F32 && dtype != UNAST_I16) return fail(UNAST_E_ARG, "unast_trim_bounds: dtype must be UNAST_F32 or UNAST_I16");
     if (workspace_bytes < unast_trim_workspace_bytes(B, max_len) || !workspace) return fail(UNAST_E_WORKSPACE, "unast_trim_bounds: workspace too small");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     cudaStream_t st = (cudaStream_t)stream;
     const int nblk = nblk_of(max_len);
     dim3 grid((nblk + 7) / 8, B);
@@ -546,13 +420,15 @@ int unast_trim_bounds(unast_ctx* c, const void* wave, int dtype, const int64_t* 
 
 int unast_frame_offsets(unast_ctx* c, const int32_t* bounds, int B, int32_t* frame_off_out, void* stream) {
     if (!c || !bounds || !frame_off_out || B <= 0) return fail(UNAST_E_ARG, "unast_frame_offsets: bad argument");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     frame_offsets_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(bounds, B, frame_off_out, c->d_err);
     CU(cudaGetLastError());
     return UNAST_OK;
 }
 
 // ---- front end ----
-size_t unast_frontend_workspace_bytes(int B) { return align256((size_t)(B + 1) * sizeof(int)); }
+size_t unast_frontend_workspace_bytes(int B) { (void)B; return 256; }    // the fused kernel needs no scratch; kept for ABI stability
 
 int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wave_off, const int32_t* bounds,
                    const int32_t* frame_off, int B, int precision, float* mel_out, int mel_layout, int T_max,
@@ -563,37 +439,25 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
     if (mel_layout != UNAST_MEL_MAJOR_PER_UTT && mel_layout != UNAST_MEL_PADDED_BTM) return fail(UNAST_E_ARG, "unast_frontend: bad mel_layout");
     if (mel_layout == UNAST_MEL_PADDED_BTM && T_max <= 0) return fail(UNAST_E_ARG, "unast_frontend: T_max required for the padded layout");
     if (!workspace || workspace_bytes < unast_frontend_workspace_bytes(B)) return fail(UNAST_E_WORKSPACE, "unast_frontend: workspace too small");
+    // the PCM16 path reads the wave as 32-bit words and prefetches it in 16-byte cp.async chunks relative to the base
+    if (dtype == UNAST_I16 && ((uintptr_t)wave & 15)) return fail(UNAST_E_ARG, "unast_frontend: an int16 wave must be 16-byte aligned");
+    if (dtype == UNAST_F32 && ((uintptr_t)wave & 3)) return fail(UNAST_E_ARG, "unast_frontend: a float32 wave must be 4-byte aligned");
+    if (((uintptr_t)mel_out & 3) || ((uintptr_t)mag_out & 3)) return fail(UNAST_E_ARG, "unast_frontend: outputs must be 4-byte aligned");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     cudaStream_t st = (cudaStream_t)stream;
-    int* tile_off = (int*)workspace;
-    if (npairs_of(c) > MEL_MAX_PAIRS) return fail(UNAST_E_ARG, "unast_frontend: filterbank plan exceeds MEL_MAX_PAIRS");
     FrontendParams P;
     P.wave = wave; P.wave_is_i16 = dtype == UNAST_I16; P.wave_off = (const long long*)wave_off; P.bounds = bounds;
-    P.frame_off = frame_off; P.tile_off = tile_off; P.B = B; P.mag_out = mag_out; P.mel_out = mel_out;
+    P.frame_off = frame_off; P.B = B; P.mag_out = mag_out; P.mel_out = mel_out;
     P.mel_layout = mel_layout; P.T_max = T_max;
-    P.mel.bfrag = c->bfrag; P.mel.pair_kb = c->pair_kb;
-    memcpy(P.mel.pair_begin, c->pair_begin, sizeof(P.mel.pair_begin));
     P.err = c->d_err;
     const bool i16 = dtype == UNAST_I16;
     if (precision == UNAST_PREC_F32) {
-        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF32::R, tile_off);
         P.win2 = i16 ? c->win2i_f : c->win2_f; P.tw1024 = c->tw_f; P.wp2 = c->wp_f;
-#if UNAST_FE32_AU
-        frontend_au_kernel<float, UNAST_FE32_AU><<<c->num_sms, UNAST_FE32_AU * 32, FeAuLayout<float, UNAST_FE32_AU>::bytes, st>>>(P, c->items);
-#elif UNAST_FE_SPECIALISED
-        FE_F32_KERNEL<<<c->num_sms, FE_F32_THREADS, FeF32::bytes, st>>>(P);
-#else
-        FE_F32_KERNEL<<<c->num_sms, FE_F32_THREADS, FeF32::bytes, st>>>(P, c->coop16);
-#endif
+        frontend_au_kernel<float, FE32_WARPS><<<c->num_sms, FE32_WARPS * 32, FeAuLayout<float, FE32_WARPS>::bytes, st>>>(P, c->items);
     } else {
-        step_offsets_kernel<<<1, 1024, 0, st>>>(frame_off, B, FeF64::R, tile_off);
         P.win2 = i16 ? (const void*)c->win2i_d : (const void*)c->win2_d; P.tw1024 = c->tw_d; P.wp2 = c->wp_d;
-#if UNAST_FE64_AU
-        frontend_au_kernel<double, UNAST_FE64_AU><<<c->num_sms, UNAST_FE64_AU * 32, FeAuLayout<double, UNAST_FE64_AU>::bytes, st>>>(P, c->items);
-#elif UNAST_FE_SPECIALISED
-        FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P);
-#else
-        FE_F64_KERNEL<<<c->num_sms, FE_F64_THREADS, FeF64::bytes, st>>>(P, c->FE_F64_COOP);
-#endif
+        frontend_au_kernel<double, FE64_WARPS><<<c->num_sms, FE64_WARPS * 32, FeAuLayout<double, FE64_WARPS>::bytes, st>>>(P, c->items);
     }
     CU(cudaGetLastError());
     return UNAST_OK;
@@ -648,6 +512,8 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     GlPlan p;
     if (!gl_plan(frames_host, B, momentum, p)) return fail(UNAST_E_ARG, "unast_griffinlim: every utterance needs >= 5 frames (librosa reflect padding)");
     if (!workspace || workspace_bytes < p.bytes) return fail(UNAST_E_WORKSPACE, "unast_griffinlim: workspace too small");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     cudaStream_t st = (cudaStream_t)stream;
     char* ws = (char*)workspace;
     int* d_frame_off = (int*)(ws + p.o_meta_i);
@@ -701,21 +567,17 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
         CU(cudaMemcpyAsync(ws + p.o_runs, runs.data(), (size_t)W * sizeof(int4), cudaMemcpyHostToDevice, st));
         P.runs = (const int4*)(ws + p.o_runs);
     }
+    cudaError_t launch_err = cudaSuccess;
     auto launch = [&]() {
-#if UNAST_GL_PK
         // programmatic dependent launch (see the kernel's prologue)
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GL_WARPS * 32); cfg.dynamicSmemBytes = GL_SMEM; cfg.stream = st;
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GL_WARPS * 32); cfg.dynamicSmemBytes = glp_smem_bytes; cfg.stream = st;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
-        if (momentum != 0.f) cudaLaunchKernelEx(&cfg, GL_KERNEL<true>, P);
-        else cudaLaunchKernelEx(&cfg, GL_KERNEL<false>, P);
-#else
-        if (momentum != 0.f) GL_KERNEL<true><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);
-        else GL_KERNEL<false><<<grid, GL_WARPS * 32, GL_SMEM, st>>>(P);
-#endif
+        const cudaError_t e = momentum != 0.f ? cudaLaunchKernelEx(&cfg, gl_pk_kernel<true>, P) : cudaLaunchKernelEx(&cfg, gl_pk_kernel<false>, P);
+        if (launch_err == cudaSuccess) launch_err = e;
     };
     P.mode = GL_INIT; P.first_iter = 1; P.ola_r = nullptr; P.ola_w = ola[1]; P.ola_z = ola[2];
     launch();
@@ -724,6 +586,7 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
         P.ola_r = ola[it % 3]; P.ola_w = ola[(it + 1) % 3]; P.ola_z = ola[(it + 2) % 3];
         launch();
     }
+    CU(launch_err);
     CU(cudaGetLastError());
 
     DeemphParams D;
@@ -754,6 +617,8 @@ int unast_mel_augment(unast_ctx* c, const float* x, int B, int T, int D, const i
     if (need_mean && (!workspace || workspace_bytes < unast_mel_augment_workspace_bytes(B)))
         return fail(UNAST_E_WORKSPACE, "unast_mel_augment: workspace too small");
     if (spans && ((uintptr_t)spans & 15)) return fail(UNAST_E_ARG, "unast_mel_augment: spans must be 16-byte aligned");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     cudaStream_t st = (cudaStream_t)stream;
     const long long slab = (long long)T * D;
     double* parts = (double*)workspace;
@@ -771,6 +636,8 @@ int unast_mel_augment(unast_ctx* c, const float* x, int B, int T, int D, const i
 
 int unast_debug_rfft(unast_ctx* c, const float* frames, int F, int precision, float* out, void* stream) {
     if (!c || !frames || !out || F <= 0) return fail(UNAST_E_ARG, "unast_debug_rfft: bad argument");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     cudaStream_t st = (cudaStream_t)stream;
     if (precision == UNAST_PREC_F64)
         debug_rfft_kernel<double><<<(F + 3) / 4, 128, 4 * xch_elems<double>() * 16, st>>>(frames, F, c->tw_d, c->wp_d, (float2*)out);
@@ -782,6 +649,8 @@ int unast_debug_rfft(unast_ctx* c, const float* frames, int F, int precision, fl
 
 int unast_debug_irfft(unast_ctx* c, const float* spec, int F, float* out, void* stream) {
     if (!c || !spec || !out || F <= 0) return fail(UNAST_E_ARG, "unast_debug_irfft: bad argument");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     debug_irfft_kernel<<<(F + 3) / 4, 128, 4 * xch_elems<float>() * 8, (cudaStream_t)stream>>>((const float2*)spec, F, c->tw_f, c->wp_f, out);
     CU(cudaGetLastError());
     return UNAST_OK;
@@ -789,6 +658,8 @@ int unast_debug_irfft(unast_ctx* c, const float* spec, int F, float* out, void* 
 
 int unast_debug_pipe_peak(unast_ctx* c, int kind, int iters, float* out, double* flop_out, void* stream) {
     if (!c || !out || iters <= 0 || kind < 0 || kind > 2) return fail(UNAST_E_ARG, "unast_debug_pipe_peak: bad argument");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     const int grid = c->num_sms * 8, block = 256;
     cudaStream_t st = (cudaStream_t)stream;
     if (kind == 0) pipe_peak_kernel<0><<<grid, block, 0, st>>>(iters, 0.999f, 0.001f, out);

@@ -13,14 +13,17 @@ stand-in modules before the import:
                 (norm='slaney', mel_scale='slaney').  This shares no code with oracle/ (which
                 restates librosa on numpy.fft), so the fixtures are a second, independent witness
                 of the librosa 0.7.1 semantics written out in SURVEY.md Appendix A.
-  soundfile  -- write() via scipy.io.wavfile.
+  soundfile  -- write() as PCM_16 (soundfile's default subtype for .wav; libsndfile rounding lrint(x * 0x7FFF)) via
+                scipy.io.wavfile.
   jiwer, data -- inert stubs (only imported at module top, never called on this path).
 
 Outputs (committed, small):
   fwd_<name>.npz   pcm (int16 input), mel [T,80], mag [T,1025], bounds of the trim
+  real_test_wav.npz  the reference's only real-speech file (Transformer-TTS/samples/test.wav, float32 WAV): wave, reference
+                   mel [T,80], every 4th row of the reference mag, trim bounds
   gl_classic.npz   mag_in [T,1025], wav = reference spectrogram2wav (60 iterations, zero phase)
   gl_fast.npz      mag_in, seed, wav = reference gl_vocoder.vocode output (librosa.griffinlim defaults,
-                   global np.random seeded with `seed` immediately before the call)
+                   global np.random seeded with `seed` immediately before the call); pcm16 = the samples that land in the file
   summary.json     shapes, known-answer checks, oracle-vs-reference deviations measured at generation time
 """
 from __future__ import annotations
@@ -153,12 +156,22 @@ def _make_librosa():
     return lib, effects, filters
 
 
+SF_LAST = {}
+
+
 def _install_stubs():
     import scipy.io.wavfile as wavfile
     lib, effects, filters = _make_librosa()
     sys.modules["librosa"], sys.modules["librosa.effects"], sys.modules["librosa.filters"] = lib, effects, filters
     sf = types.ModuleType("soundfile")
-    sf.write = lambda path, data, rate: wavfile.write(path, rate, np.asarray(data))
+
+    def sf_write(path, data, rate):
+        # python-soundfile: default subtype for .wav is PCM_16 whatever the dtype; libsndfile (normalised floats, clipping
+        # off) stores lrint(x * 0x7FFF) truncated to 16 bits.  The float data is kept so that the fixture can hold both.
+        d = np.asarray(data, np.float64)
+        SF_LAST["data"] = d.copy()
+        wavfile.write(path, rate, (np.rint(d * 32767.0).astype(np.int64) & 0xFFFF).astype(np.uint16).view(np.int16))
+    sf.write = sf_write
     sys.modules["soundfile"] = sf
     jw = types.ModuleType("jiwer")
     jw.wer = lambda *a, **k: 0.0
@@ -217,6 +230,10 @@ def main():
     mel, mag = ref_utils.get_spectrograms(tw)
     omel, omag = so.get_spectrograms(tw)
     y_tw, _ = so.load(tw)
+    _, b_tw = sys.modules["librosa"].effects.trim(y_tw)
+    rows = np.arange(0, mag.shape[0], 4)                                  # every 4th magnitude row keeps the fixture small
+    np.savez_compressed(os.path.join(HERE, "real_test_wav.npz"), wave=np.asarray(y_tw, np.float32), mel=np.ascontiguousarray(mel),
+                        mag_rows=rows.astype(np.int32), mag=np.ascontiguousarray(mag[rows]), bounds=np.asarray(b_tw, np.int32))
     summary["cases"]["test_wav"] = {
         "samples": int(y_tw.size), "known_answer_samples_275x399": bool(y_tw.size == 275 * 399),
         "T": int(mel.shape[0]), "oracle_T": int(omel.shape[0]),
@@ -252,11 +269,13 @@ def main():
     np.random.seed(seed)
     ref_glv.vocode(os.path.join(tmp, "list.csv"), mdir, odir)
     import scipy.io.wavfile as wavfile
-    rate, wav_fast = wavfile.read(os.path.join(odir, "utt0.wav"))
+    rate, pcm_fast = wavfile.read(os.path.join(odir, "utt0.wav"))
+    assert pcm_fast.dtype == np.int16
+    wav_fast = SF_LAST["data"]                                          # the float64 array gl_vocoder.py:34 hands to sf.write
     np.random.seed(seed)
     owav_fast = so.vocode_one(mag_fast)
     np.savez_compressed(os.path.join(HERE, "gl_fast.npz"), mag_in=mag_fast, seed=np.int64(seed),
-                        wav=wav_fast.astype(np.float32))
+                        wav=wav_fast.astype(np.float32), pcm16=pcm_fast)
     summary["cases"]["gl_fast"] = {
         "T": 40, "n_iter": 32, "momentum": 0.99, "rate": int(rate), "len": int(wav_fast.size), "oracle_len": int(owav_fast.size),
         "oracle_vs_reference_snr_db": _snr_db(wav_fast, owav_fast) if wav_fast.size == owav_fast.size else None}

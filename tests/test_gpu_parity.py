@@ -330,6 +330,8 @@ def test_vocode_cli_files(tmp_path):
     for i, m in enumerate(mags):
         y, rate = wavio.read_wav(str(tmp_path / "out" / ("utt%d.wav" % i)))
         ref = so.vocode_one(m).astype(np.float32)                                 # draws rand(1025, T) in list order
+        assert y.dtype == np.int16                                                # sf.write default subtype: PCM_16
+        y = y.astype(np.float32) / np.float32(32767.0)
         assert rate == 22050 and y.shape == ref.shape and snr_db(ref, y) >= GL_SNR_DB
 
 
@@ -505,3 +507,96 @@ def test_loader_batch_then_specaugment_like_the_supervised_step():
     spans = so.specaugment_spans(mel_len.cpu().numpy())
     want = so.specaugment_apply(mel.cpu().numpy(), spans)
     assert np.abs(aug.cpu().numpy() - want).max() <= 6e-8
+
+
+# ------------------------------------------------------------------------------------------------
+# round 2: real speech, benchmark-scale Griffin-Lim, long waveforms, gradients, device handling
+# ------------------------------------------------------------------------------------------------
+def test_real_speech_fixture_through_the_cuda_path(golden):
+    """The reference's only real-speech file (Transformer-TTS/samples/test.wav, float32 input path) against the mel /
+    mag its own get_spectrograms produced (tests/golden/make_golden.py)."""
+    from unast_b200 import utils as U
+    g = golden("real_test_wav")
+    (mel, mag, b), = U.spectrograms_from_waves([g["wave"]], return_bounds=True)
+    assert b == tuple(int(v) for v in g["bounds"]) and mel.shape == g["mel"].shape
+    assert np.abs(mel - g["mel"]).max() <= TOL
+    assert np.abs(mag[g["mag_rows"]] - g["mag"]).max() <= TOL
+    omel, omag = so.spectrograms_from_wave(g["wave"])                             # and every bin against the oracle
+    assert np.abs(mag - omag).max() <= TOL and np.abs(mel - omel).max() <= TOL
+
+
+def test_griffin_lim_benchmark_scale_batch():
+    """C3 as benchmarked: 64 spectrograms of LJSpeech-shaped lengths in ONE call, 100 classic iterations from zero
+    phase; four of them (shortest, longest, first, last) against the oracle."""
+    from unast_b200 import synth, utils as U
+    durs = synth.ljspeech_durations(64, seed=2)
+    waves = [synth.speech_like(float(d), 3000 + i) for i, d in enumerate(durs)]
+    (mags) = [m for _, m in U.spectrograms_from_waves(waves)]
+    outs = U.spectrogram2wav_batch(mags, n_iter=100, do_trim=False)
+    pick = sorted({0, 63, int(np.argmin(durs)), int(np.argmax(durs))})
+    for i in pick:
+        ref = so.spectrogram2wav(mags[i], iters=100, return_untrimmed=True)
+        _check_gl(outs[i], ref, so.denormalise(mags[i]))
+
+
+def test_griffin_lim_long_waveform():
+    """One 60 s spectrogram (4,811 frames: hundreds of warp runs and seams inside one utterance), 30 iterations."""
+    from unast_b200 import synth, utils as U
+    w = np.concatenate([synth.speech_like(10.0, 80 + i) for i in range(6)])
+    (mel, mag), = U.spectrograms_from_waves([w], do_trim=False)
+    y, = U.spectrogram2wav_batch([mag], n_iter=30, do_trim=False)
+    ref = so.spectrogram2wav(mag, iters=30, return_untrimmed=True)
+    _check_gl(y, ref, so.denormalise(mag))
+
+
+def test_noise_fn_lets_gradients_through():
+    """utils.py:49 is `to_noise * zero_mask`: differentiable, and applied to the embedded phonemes (network.py:431)."""
+    torch = _torch()
+    from unast_b200.augment import noise_fn
+    x = torch.randn(4, 33, 16, device="cuda", requires_grad=True)
+    torch.manual_seed(5)
+    y = noise_fn(x, mask_p=.3)
+    torch.manual_seed(5)
+    keep = torch.bernoulli(torch.zeros(4, 33, device="cuda").fill_(.7)).unsqueeze(-1)
+    w = torch.randn_like(x)
+    (y * w).sum().backward()
+    assert torch.equal(y.detach(), x.detach() * keep) and torch.equal(x.grad, w * keep)
+    with pytest.raises(TypeError):
+        noise_fn(x.double())
+
+
+def test_unaligned_pcm16_view_is_rejected(engine):
+    """The PCM16 path prefetches 16-byte chunks relative to the base pointer: a sliced int16 tensor must be refused
+    (UNAST_E_ARG), not fault."""
+    torch = _torch()
+    from unast_b200 import synth
+    w = torch.from_numpy(synth.to_pcm16(synth.speech_like(1.5, 90))).cuda()
+    v = w[3:]
+    off = torch.tensor([0, v.numel()], dtype=torch.int64, device="cuda")
+    bounds = torch.tensor([[0, v.numel()]], dtype=torch.int32, device="cuda")
+    fo = engine.frame_offsets(bounds)
+    with pytest.raises(Exception):
+        engine.frontend(v, off, bounds, fo, int(fo[-1]))
+
+
+def test_engine_on_a_non_current_device():
+    """unast_create / every entry point select the context's device and restore the caller's."""
+    torch = _torch()
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from unast_b200.engine import SpectralEngine
+    from unast_b200 import synth
+    assert torch.cuda.current_device() == 0
+    eng = SpectralEngine(1)
+    assert torch.cuda.current_device() == 0
+    w = synth.speech_like(1.5, 91)
+    wave = torch.from_numpy(w).to("cuda:1")
+    off = torch.tensor([0, w.size], dtype=torch.int64, device="cuda:1")
+    with torch.cuda.device(1):
+        bounds = eng.trim_bounds(wave, off, w.size)
+        fo = eng.frame_offsets(bounds)
+        eng.check()
+        mel, mag = eng.frontend(wave, off, bounds, fo, int(fo.cpu()[-1]))
+    assert torch.cuda.current_device() == 0
+    omel, omag = so.spectrograms_from_wave(w)
+    assert np.abs(mag.cpu().numpy() - omag).max() <= TOL

@@ -61,6 +61,23 @@ def test_wav_roundtrip_pcm16_and_float32(tmp_path):
     assert r2 == 22050 and np.array_equal(d2, y)
 
 
+def test_vocode_output_format_is_pcm16(tmp_path):
+    """gl_vocoder.py:34 `sf.write(path, wav, ap.sr)`: soundfile's default subtype for .wav is PCM_16 (tag 1, 16 bits),
+    samples lrint(x * 0x7FFF) with wrap-around (libsndfile, clipping off)."""
+    import struct
+    y = np.array([0.0, 0.5, -0.5, 1.0, -1.0, 0.25 + 1e-6, 1.00002, 1.5 / 32767.0, 2.5 / 32767.0], np.float64)
+    p = str(tmp_path / "v.wav")
+    wavio.write_wav_pcm16(p, y)
+    b = open(p, "rb").read()
+    tag, nch, rate, brate, align, bits = struct.unpack("<HHIIHH", b[20:36])
+    assert (tag, nch, rate, brate, align, bits) == (1, 1, 22050, 44100, 2, 16) and b[36:40] == b"data"
+    q, _ = wavio.read_wav(p)
+    assert q.dtype == np.int16
+    assert q.tolist() == [0, 16384, -16384, 32767, -32767, 8192, -32768, 2, 2]    # round half to even; > 1.0 wraps
+    import scipy.io.wavfile as sw
+    assert np.array_equal(sw.read(p)[1], q)
+
+
 def test_wav_wrong_rate_raises(tmp_path):
     p = str(tmp_path / "c.wav")
     synth.write_wav_pcm16(p, np.zeros(100, np.int16), rate=16000)

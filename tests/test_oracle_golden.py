@@ -160,3 +160,96 @@ def test_specaugment_host_draws_and_error_match_reference(golden):
     with pytest.raises(ValueError) as e:
         draw_specaugment_spans(np.full(6, 10))
     assert "ValueError: %s" % e.value == str(g["short_error"])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Independent witnesses (no code shared with oracle/): scipy / torch for the inverse transform, brute-force O(N T)
+# restatements of librosa.filters.window_sumsquare and librosa.effects.trim straight from SURVEY.md Appendix A.
+# ---------------------------------------------------------------------------------------------------------------
+def _speechy(n, seed):
+    rs = np.random.RandomState(seed)
+    t = np.arange(n) / 22050.0
+    y = sum(a * np.sin(2 * np.pi * f * t + p) for a, f, p in zip(rs.rand(12) * 0.1, 100 + 2000 * rs.rand(12), 6.28 * rs.rand(12)))
+    return (y * (0.5 + 0.5 * np.sin(2 * np.pi * 3 * t)) + 1e-3 * rs.randn(n)).astype(np.float32)
+
+
+def test_real_speech_fixture_matches_reference(golden):
+    """samples/test.wav of the reference (float32 WAV, 275 * 399 samples) through its own get_spectrograms."""
+    g = golden("real_test_wav")
+    assert g["wave"].size == 275 * 399
+    mel, mag, b = so.spectrograms_from_wave(g["wave"], return_bounds=True)
+    assert b == tuple(int(v) for v in g["bounds"]) and mel.shape == g["mel"].shape
+    assert np.abs(mel - g["mel"]).max() <= 5e-6
+    assert np.abs(mag[g["mag_rows"]] - g["mag"]).max() <= 5e-6
+
+
+def test_istft_against_torch_and_scipy():
+    """oracle.istft vs torch.istft (float64) on every sample and vs scipy.signal.istft on interior samples."""
+    import scipy.signal
+    import torch
+    y = _speechy(275 * 60, 5)
+    X = so.stft(y)                                                               # [1025, 61] complex64
+    mine = so.istft(X)
+    assert mine.size == 275 * 60
+    win = torch.zeros(2048, dtype=torch.float64)
+    win[473:473 + 1102] = torch.from_numpy(0.5 - 0.5 * np.cos(2 * np.pi * np.arange(1102) / 1102))
+    ref = torch.istft(torch.from_numpy(X.astype(np.complex128)), n_fft=2048, hop_length=275, win_length=2048, window=win,
+                      center=True, length=275 * 60).numpy()
+    assert np.abs(mine - ref).max() <= 2e-6
+    # scipy: boundary=True trims nperseg // 2 like center=True; its scaling is window.sum() and it normalises by the
+    # window-sum envelope as librosa does (interior samples only: scipy treats the edges differently)
+    w = win.numpy()
+    _, ys = scipy.signal.istft(X.astype(np.complex128) / w.sum(), fs=1.0, window=w, nperseg=2048, noverlap=2048 - 275, nfft=2048,
+                               input_onesided=True, boundary=True)
+    n = min(ys.size, mine.size)
+    assert np.abs(mine[2048:n - 2048] - ys[2048:n - 2048]).max() <= 2e-6
+
+
+def test_window_sumsquare_brute_force():
+    """Appendix A.3: wss[n] = sum_t hann^2[n - 275 t - 473] in float32 accumulation, by direct summation."""
+    T = 23
+    wss = so.window_sumsquare(T)
+    h2 = (0.5 - 0.5 * np.cos(2 * np.pi * np.arange(1102) / 1102)) ** 2
+    n = 2048 + 275 * (T - 1)
+    assert wss.shape == (n,) and wss.dtype == np.float32
+    brute = np.zeros(n, np.float64)
+    for q in range(n):
+        for t in range(T):
+            i = q - 275 * t - 473
+            if 0 <= i < 1102:
+                brute[q] += h2[i]
+    assert np.abs(wss - brute).max() <= 1e-5 * brute.max()
+    assert np.all((wss > np.finfo(np.float32).tiny) == (brute > 0))              # same support: same samples are normalised
+
+
+def test_trim_brute_force():
+    """Appendix A.5 by direct loops (reflect index arithmetic written out, no np.pad / framing helper)."""
+    rs = np.random.RandomState(9)
+    y = np.concatenate([1e-5 * rs.randn(3000), 0.3 * rs.randn(9000), 1e-5 * rs.randn(2500)]).astype(np.float32)
+    N = y.size
+    nfr = 1 + N // 512
+    mse = np.zeros(nfr)
+    for f in range(nfr):
+        acc = 0.0
+        for j in range(2048):
+            i = f * 512 + j - 1024
+            if i < 0:
+                i = -i
+            if i >= N:
+                i = 2 * (N - 1) - i
+            acc += float(y[i]) ** 2
+        mse[f] = acc / 2048
+    db = 10 * np.log10(np.maximum(1e-10, mse)) - 10 * np.log10(max(1e-10, mse.max()))
+    nz = np.flatnonzero(db > -60)
+    expect = (int(nz[0]) * 512, min(N, (int(nz[-1]) + 1) * 512))
+    assert so.trim_bounds(y) == expect
+    assert 1000 < expect[0] <= 3072 and 12000 <= expect[1] < 14000              # the silences really were trimmed (frames reach +-1024)
+
+
+def test_pcm16_fixture_of_vocode(golden):
+    """gl_vocoder.py:34 sf.write -> PCM_16: the samples in the reference-written file vs the float data handed to it."""
+    g = golden("gl_fast")
+    assert g["pcm16"].dtype == np.int16 and g["pcm16"].shape == g["wav"].shape
+    d = g["pcm16"].astype(np.float64) - g["wav"].astype(np.float64) * 32767.0
+    d = (d + 32768.0) % 65536.0 - 32768.0                                        # clipping is off by default: |x| > 1 wraps
+    assert np.abs(d).max() <= 0.51

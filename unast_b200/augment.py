@@ -48,17 +48,39 @@ def specaugment(mel, mel_len, freq_mask=20, time_mask=100, replace_with_zero=Fal
     return eng.mel_augment(x.contiguous(), spans=torch.from_numpy(spans).to(eng.device), replace_with_zero=replace_with_zero)
 
 
+class _RowMask(torch.autograd.Function):
+    """y = x * keep[..., None] through unast_mel_augment, forward and backward (d/dx = keep): the reference's
+    ``to_noise * zero_mask`` (src/utils.py:49) is differentiable and is applied to tensors that require grad
+    (``embedded_phonemes`` at src/network.py:431,521), so the drop-in must let gradients through."""
+
+    @staticmethod
+    def forward(ctx, x, keep):
+        ctx.save_for_backward(keep)
+        return get_engine().mel_augment(x.detach().contiguous(), keep=keep)
+
+    @staticmethod
+    def backward(ctx, grad):
+        keep, = ctx.saved_tensors
+        return get_engine().mel_augment(grad.contiguous(), keep=keep), None
+
+
 def noise_fn(to_noise, mask_p=.3, swap_p=0):
-    """src/utils.py:40-49: whole time steps of a [batch, seq_len, dim] tensor zeroed with probability ``mask_p``
-    (``swap_p`` does nothing in the reference either)."""
+    """src/utils.py:40-49 (callers: src/network.py:205,307 on the speech prenet output, :431,:521 on the embedded
+    phonemes): whole time steps of a float32 [batch, seq_len, dim] tensor zeroed with probability ``mask_p``
+    (``swap_p`` does nothing in the reference either).  Differentiable like the reference's multiply."""
     eng = get_engine()
+    if to_noise.dim() != 3 or to_noise.dtype != torch.float32:
+        raise TypeError("noise_fn: expected a float32 [batch, seq_len, dim] tensor, got %s %s" % (to_noise.dtype, tuple(to_noise.shape)))
     gen = torch.zeros((to_noise.shape[0], to_noise.shape[1]), device=to_noise.device)
     gen.fill_(1 - mask_p)
     zero_mask = torch.bernoulli(gen)
-    x = to_noise.detach()
+    x = to_noise
     if x.device != eng.device:
         x, zero_mask = x.to(eng.device), zero_mask.to(eng.device)
-    return eng.mel_augment(x.contiguous(), keep=zero_mask.contiguous())
+    zero_mask = zero_mask.contiguous()
+    if x.requires_grad:
+        return _RowMask.apply(x, zero_mask)
+    return eng.mel_augment(x.contiguous(), keep=zero_mask)
 
 
 def specaugment_noise(mel, mel_len, freq_mask=20, time_mask=100, replace_with_zero=False, mask_p=.3):

@@ -15,7 +15,7 @@ import numpy as np
 
 from . import audio_parameters as ap
 from .utils import _gl_batch
-from .wavio import write_wav_float32
+from .wavio import write_wav_float32, write_wav_pcm16
 
 GL_ITERS = 32        # librosa.griffinlim default n_iter
 GL_MOMENTUM = 0.99   # librosa.griffinlim default momentum
@@ -39,7 +39,11 @@ def vocode_arrays(mags, n_iter=GL_ITERS, momentum=GL_MOMENTUM, angles0=None, ran
     return _gl_batch(mags, n_iter, momentum, angles0, ap.power, True, do_trim)
 
 
-def vocode(list_file, mels_dir, out_dir, batch_size=64):
+def vocode(list_file, mels_dir, out_dir, batch_size=64, subtype="PCM_16"):
+    """gl_vocoder.py:10-34.  ``subtype``: "PCM_16" (soundfile's default for .wav, what the reference writes) or "FLOAT"."""
+    if subtype not in ("PCM_16", "FLOAT"):
+        raise ValueError("subtype must be 'PCM_16' or 'FLOAT'")
+    write = write_wav_pcm16 if subtype == "PCM_16" else write_wav_float32
     if not os.path.exists(out_dir):
         os.makedirs(out_dir)
     names = _read_list(list_file)
@@ -48,7 +52,7 @@ def vocode(list_file, mels_dir, out_dir, batch_size=64):
         mags = [np.load(os.path.join(mels_dir, "{}.mag.npy".format(n))) for n in chunk]
         wavs = vocode_arrays(mags)
         for n, wav in zip(chunk, wavs):
-            write_wav_float32(os.path.join(out_dir, "{}.wav".format(n)), wav, ap.sr)
+            write(os.path.join(out_dir, "{}.wav".format(n)), wav, ap.sr)
 
 
 if __name__ == "__main__":

@@ -50,8 +50,23 @@ def read_wav(path, expect_sr=ap.sr):
     return np.ascontiguousarray(y), rate
 
 
+def write_wav_pcm16(path, y, rate=ap.sr):
+    """16-bit PCM WAV, what ``sf.write(path, wav, sr)`` (gl_vocoder.py:34) produces: python-soundfile's default subtype
+    for ``.wav`` is PCM_16 whatever the array dtype, and libsndfile converts floats (normalised, clipping off -- the
+    defaults) as ``lrint(x * 0x7FFF)`` truncated to 16 bits (libsndfile src/pcm.c, d2les_array: round half to even, values
+    outside [-1, 1] wrap).  libsndfile is not installable in this image, so this restates its published source; no test
+    here pins it against the real library."""
+    v = np.rint(np.asarray(y, dtype=np.float64) * 32767.0).astype(np.int64)
+    data = (v & 0xFFFF).astype("<u2").tobytes()
+    with open(path, "wb") as fh:
+        fh.write(b"RIFF" + struct.pack("<I", 36 + len(data)) + b"WAVE")
+        fh.write(b"fmt " + struct.pack("<IHHIIHH", 16, 1, 1, rate, rate * 2, 2, 16))
+        fh.write(b"data" + struct.pack("<I", len(data)) + data)
+
+
 def write_wav_float32(path, y, rate=ap.sr):
-    """Float32 WAV, as ``sf.write(path, wav, sr)`` (gl_vocoder.py:34) / scipy.io.wavfile.write produce."""
+    """IEEE float32 WAV (``sf.write(..., subtype='FLOAT')`` / ``scipy.io.wavfile.write`` as Transformer-TTS
+    synthesis.py:50 uses): opt-in, not what gl_vocoder.py:34 writes."""
     y = np.ascontiguousarray(np.asarray(y, dtype="<f4"))
     data = y.tobytes()
     with open(path, "wb") as fh:

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define UNAST_ABI_VERSION 1
+#define UNAST_ABI_VERSION 2
 
 #define UNAST_OK 0
 #define UNAST_E_CUDA (-1)      /* a CUDA runtime call failed */
@@ -106,6 +106,53 @@ size_t unast_griffinlim_workspace_bytes(const int32_t* frames_host, int B, float
 int unast_griffinlim(unast_ctx* ctx, const float* mag_norm, const int32_t* frames_host, int B, int n_iter,
                      float momentum, const float* angles0, float power, int deemphasis, float* wav_out,
                      int32_t* bounds_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- one long waveform sharded over GPUs by frame range (the loop of utils.py:309-320) ------
+ * A *fragment* is the contiguous range [t0, t0 + n) of the frames of an utterance of tglob frames (n >= 9 unless the
+ * fragment is the whole utterance).  Where two fragments of one utterance meet, the 827 samples their frames share (a
+ * *linked seam*) exist in both fragments' overlap-add buffers; every iteration both sides add their partial sums into
+ * both copies (plain stores / atomics over NVLink peer mappings) and publish their progress in the partner's mailbox.
+ * No collective, no host round trip; the kernel is one persistent cooperative launch per call.
+ *   side 0 = the seam at the fragment's first frame, side 1 = the seam after its last frame;
+ *   peer_ola[k] = address, in the PARTNER's copy of rotating buffer k, of the seam's first sample: the partner's
+ *                 workspace base + layout[k] + 4 * (partner's pad_off[fragment'] + 473 (+ 275 n' for its side 1)),
+ *                 pad_off = prefix sum of 2048 + 275 (n - 1) over the partner's fragments;
+ *   peer_mail   = address of the partner's mailbox slot for this link (its workspace base + layout[3] + 4 * slot);
+ *   my_mail     = this side's mailbox slot (< 16) -- the partner's peer_mail must point at it.
+ * epoch >= 1 must be the same on both sides and grow by at least n_iter + 2 from call to call (mailboxes are never
+ * reset; a workspace must be zero-filled before its first use -- unast_peer_alloc does that).
+ * raw_out receives, fragment after fragment, the samples each fragment owns (unast_griffinlim_fragment_samples) of
+ * istft(S * angles): normalised by the window-sum envelope, NOT de-emphasised or trimmed (both need the whole
+ * waveform: gather, then unast_deemph_trim). */
+typedef struct unast_gl_link {
+    int32_t fragment;
+    int32_t side;
+    void* peer_ola[3];
+    void* peer_mail;
+    int32_t my_mail;
+} unast_gl_link;
+
+/* layout_out[5] = byte offsets of the three rotating overlap-add buffers and of the mailbox array inside a workspace
+ * for these fragment sizes, and the workspace size (== unast_griffinlim_workspace_bytes).  Host-only, deterministic. */
+int unast_griffinlim_layout(const int32_t* frames_host, int B, float momentum, size_t* layout_out);
+int unast_griffinlim_fragment_samples(int32_t t0, int32_t n, int32_t tglob, int64_t* first_out, int64_t* end_out);
+int unast_griffinlim_fragments(unast_ctx* ctx, const float* mag_norm, const int32_t* frames_host, const int32_t* t0_host,
+                               const int32_t* tglob_host, int B, const unast_gl_link* links_host, int n_links, int epoch,
+                               int n_iter, float momentum, const float* angles0, float power, float* raw_out,
+                               void* workspace, size_t workspace_bytes, void* stream);
+
+/* scipy.signal.lfilter([1], [1, -0.97]) in float64 (utils.py:301) and librosa.effects.trim bounds (utils.py:304) of B
+ * plain waveforms x (float32, off[B+1] int64 device offsets): the epilogue of the sharded run after the gather. */
+size_t unast_deemph_trim_workspace_bytes(int B, int max_len);
+int unast_deemph_trim(unast_ctx* ctx, const float* x, const int64_t* off, int B, int max_len, int deemphasis,
+                      float* wav_out, int32_t* bounds_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Device memory other processes on the node can map (CUDA IPC; peer access over NVLink is enabled on open).
+ * handle64: 64 bytes to hand to the peer process (e.g. torch.distributed.all_gather_object). */
+int unast_peer_alloc(unast_ctx* ctx, size_t bytes, void** dptr_out, unsigned char* handle64_out);
+int unast_peer_open(unast_ctx* ctx, const unsigned char* handle64, void** dptr_out);
+int unast_peer_close(unast_ctx* ctx, void* dptr);
+int unast_peer_free(unast_ctx* ctx, void* dptr);
 
 /* ---- next row: the masking ops applied to the padded mel batch ----------- */
 

@@ -600,3 +600,34 @@ def test_engine_on_a_non_current_device():
     assert torch.cuda.current_device() == 0
     omel, omag = so.spectrograms_from_wave(w)
     assert np.abs(mag.cpu().numpy() - omag).max() <= TOL
+
+
+def test_sharded_griffin_lim_protocol_emulated_on_one_gpu():
+    """C5 inverse: one long spectrogram cut into fragments with linked seams (what the ranks of the sharded run do over
+    NVLink), emulated in one launch.  One fragment == the ordinary path bit for bit; 2 / 3 / 5 fragments differ from it
+    only by the summation order at the run boundaries."""
+    torch = _torch()
+    from unast_b200 import longform as LF, synth, utils as U
+    w = np.concatenate([synth.speech_like(8.0, 120 + i) for i in range(3)])            # 24 s
+    (mel, mag), = U.spectrograms_from_waves([w], do_trim=False)
+    n_iter = 12
+    base, = U._gl_batch([mag], n_iter, 0.0, None, 1.2, False, False)                  # normalised, no de-emphasis / trim
+    mag_d = torch.from_numpy(mag).cuda()
+    one = LF.griffinlim_fragments_emulated(mag_d, 1, n_iter).cpu().numpy()
+    assert np.array_equal(one, base)
+    for world in (2, 3, 5):
+        y = LF.griffinlim_fragments_emulated(mag_d, world, n_iter).cpu().numpy()
+        assert y.shape == base.shape and snr_db(base, y) >= 80.0
+    rs = np.random.RandomState(4)                                                      # momentum variant, seeded phases
+    a0 = np.exp(2j * np.pi * rs.rand(mag.shape[0], 1025)).astype(np.complex64)
+    a0_d = torch.from_numpy(a0).cuda()
+    ref = LF.griffinlim_fragments_emulated(mag_d, 1, 8, momentum=0.99, angles0=a0_d).cpu().numpy()
+    y = LF.griffinlim_fragments_emulated(mag_d, 4, 8, momentum=0.99, angles0=a0_d).cpu().numpy()
+    assert snr_db(ref, y) >= 80.0
+    # epilogue of the sharded run: de-emphasis + trim of the gathered waveform == the ordinary call's
+    full, = U.spectrogram2wav_batch([mag], n_iter=n_iter, do_trim=True)
+    eng = U.get_engine()
+    L = base.size
+    wav, bounds = eng.deemph_trim(torch.from_numpy(base).cuda(), torch.tensor([0, L], dtype=torch.int64, device="cuda"), L)
+    s, e = (int(v) for v in bounds.cpu().numpy()[0])
+    assert np.array_equal(wav.cpu().numpy()[s:e], full)

@@ -129,7 +129,7 @@ def test_c_abi_exports_every_declared_symbol():
     lib = ctypes.CDLL(_lib.LIB_PATH)
     for name in declared:
         assert hasattr(lib, name), "library does not export " + name
-    assert lib.unast_abi_version() == 1                                               # no compute call without a GPU
+    assert lib.unast_abi_version() == 2                                               # no compute call without a GPU
 
 
 def test_product_fails_loudly_without_gpu():

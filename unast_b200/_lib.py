@@ -33,12 +33,29 @@ SYMBOLS = [
     ("unast_frontend", _i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _sz, _vp]),
     ("unast_griffinlim_workspace_bytes", _sz, [_vp, _i, _f]),
     ("unast_griffinlim", _i, [_vp, _vp, _vp, _i, _i, _f, _vp, _f, _i, _vp, _vp, _vp, _sz, _vp]),
+    ("unast_griffinlim_layout", _i, [_vp, _i, _f, _vp]),
+    ("unast_griffinlim_fragment_samples", _i, [_i, _i, _i, _vp, _vp]),
+    ("unast_griffinlim_fragments", _i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _f, _vp, _f, _vp, _vp, _sz, _vp]),
+    ("unast_deemph_trim_workspace_bytes", _sz, [_i, _i]),
+    ("unast_deemph_trim", _i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    ("unast_peer_alloc", _i, [_vp, _sz, C.POINTER(_vp), _vp]),
+    ("unast_peer_open", _i, [_vp, _vp, C.POINTER(_vp)]),
+    ("unast_peer_close", _i, [_vp, _vp]),
+    ("unast_peer_free", _i, [_vp, _vp]),
     ("unast_mel_augment_workspace_bytes", _sz, [_i]),
     ("unast_mel_augment", _i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
     ("unast_debug_rfft", _i, [_vp, _vp, _i, _i, _vp, _vp]),
     ("unast_debug_irfft", _i, [_vp, _vp, _i, _vp, _vp]),
     ("unast_debug_pipe_peak", _i, [_vp, _i, _i, _vp, C.POINTER(C.c_double), _vp]),
 ]
+
+
+
+class GlLink(C.Structure):
+    """unast_gl_link of include/unast_spectral.h."""
+    _fields_ = [("fragment", C.c_int32), ("side", C.c_int32), ("peer_ola", C.c_void_p * 3), ("peer_mail", C.c_void_p),
+                ("my_mail", C.c_int32)]
+
 
 _lib = None
 
@@ -63,7 +80,7 @@ def load():
         fn = getattr(lib, name)          # AttributeError here means header and library disagree
         fn.restype = restype
         fn.argtypes = argtypes
-    if lib.unast_abi_version() != 1:
+    if lib.unast_abi_version() != 2:
         raise ImportError("libunast_spectral ABI version mismatch")
     _lib = lib
     return lib

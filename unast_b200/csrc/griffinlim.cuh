@@ -27,36 +27,46 @@
 
 namespace unast {
 
-enum GlMode : int { GL_INIT = 0, GL_ITER = 1 };
-
 constexpr int GL_EDGE_L = 2404;            // left-edge envelope table: padded positions [0, 2404)
 constexpr int GL_EDGE_R = 2204;            // right-edge table: u + 1100, u = q - 473 - 275 (T - 1) in [-1100, 1104)
 constexpr int GL_TABLE_MIN_T = 12;         // utterances shorter than this use the exact (slow) envelope on edge frames
+constexpr int GL_MAX_LINKS = 16;
+
+// A linked seam: the 827 samples shared by the last frames of one fragment and the first frames of the next one when
+// the two live in different overlap-add buffers (another GPU's memory over NVLink, or -- in the single-GPU emulation of
+// the multi-rank run -- another fragment of the same launch).  Both sides add their partial sums into both copies.
+struct GlLink {
+    float* peer[3];              // partner's copy of rotating buffer k, offset so that peer[k][q] pairs with local index q
+    int* push;                   // partner's mailbox (peer memory): this side's progress is stored there
+    const int* poll;             // this side's mailbox (local memory): the partner's progress
+};
 
 struct GlParams {
     const float* S;              // [sum T][S_STRIDE] target magnitude (already raised to `power`)
-    const int* frame_off;        // [B+1]
-    const long long* pad_off;    // [B+1] prefix sum of Lp_b = 2048 + 275 (T_b - 1)
+    const int* frame_off;        // [B+1] local prefix sum of the fragments' frame counts
+    const long long* pad_off;    // [B+1] prefix sum of Lp_b = 2048 + 275 (n_b - 1)
+    const int* t0;               // [B] index of the fragment's first frame inside its utterance (0 for whole utterances)
+    const int* Tg;               // [B] frames of the whole utterance the fragment belongs to
     int B;
-    int total_frames;
-    const int4* runs;            // [gridDim.x * GL_WARPS] (first frame, end frame, utterance of the first frame) per warp
-    const long long* cost_off;   // [B+1] prefix sum of the utterances' cost (interior frame 4, edge frame 5): run partition
-    const float* ola_r;          // read buffer  (unused in GL_INIT)
-    float* ola_w;                // write buffer
-    float* ola_z;                // buffer whose seams are zeroed for the next iteration
+    int n_runs;                  // active warps (each owns a non-empty run of frames)
+    const int4* runs;            // [n_runs] (first frame, end frame, fragment of the first frame, link_l + 1 | (link_r + 1) << 16)
+    float* ola[3];               // rotating overlap-add buffers: iteration `it` reads [it % 3], writes [(it + 1) % 3], re-zeroes
+                                 // the seams of [(it + 2) % 3]
+    int n_iter;
+    int* done;                   // [n_runs] epoch + number of iterations warp w has completed (incl. the initial inverse)
+    int epoch;                   // base value of this call's progress counters (counters are never reset)
+    int* abort;                  // set when a wait timed out; every wait loop leaves when it is set
+    int* err;
+    GlLink links[GL_MAX_LINKS];
     float2* tprev;               // [sum T][1025] previous STFT estimate (momentum variant) or nullptr
-    const float2* angles0;       // [sum T][1025] initial unit phases (GL_INIT) or nullptr = zero phase
+    const float2* angles0;       // [sum T][1025] initial unit phases or nullptr = zero phase
     float alpha;                 // momentum / (1 + momentum); 0 selects classic Griffin-Lim
-    int mode;
-    int first_iter;              // momentum: treat tprev as zero (librosa starts from rebuilt = 0)
     const float2* wa2;           // interior frames: (w[2n], w[2n+1]) / 2 / window-sum envelope (periodic part)
     const float2* win2;          // (w[2n], w[2n+1]) / 2
     const float2* wini2;         // (w[2n], w[2n+1]) / 2048 (irfft scaling folded into the synthesis window)
-    const float2* tw1024;
-    const float4* tw4;           // packed layout of tw1024 for fft_pk.cuh: [16][32] (c[2m], c[2m+1], s[2m], s[2m+1])
+    const float4* tw4;           // packed W1024^(lane k1) for fft_pk.cuh: [16][32] (c[2m], c[2m+1], s[2m], s[2m+1])
     const float4* tw4a;          // ... for pairs (j, j + 16): [16][32] (c[j], c[j+16], s[j], s[j+16])
     const float4* wp4;           // packed wp2: [8][32] (wx[ka], wx[ka+32], wy[ka], wy[ka+32]), ka = lane + 64 m
-    const float2* wp2;
     const float2* phi;           // [1025] exp(+2 pi i 473 k / 2048): shift phase applied to the initial spectrum
     const float* rinv_l;         // [GL_EDGE_L] 1 / envelope at padded position q (left edge)
     const float* rinv_r;         // [GL_EDGE_R] 1 / envelope at u + 1100 (right edge)

@@ -218,4 +218,35 @@ __global__ void deemph_kernel(const DeemphParams P) {
     }
 }
 
+// The samples a fragment owns (sharded long-form Griffin-Lim): out = ola / window-sum envelope, no de-emphasis.
+// Fragment b = frames [t0, t0 + n) of an utterance of Tg frames owns wave samples [275 t0 - 551, 275 (t0 + n) - 551),
+// clipped to the utterance; its local overlap-add buffer starts at padded position 275 t0.
+struct GlExtractParams {
+    const float* ola;
+    const int* frame_off;
+    const long long* pad_off;
+    const int* t0;
+    const int* Tg;
+    const long long* raw_off;    // [B+1] prefix sum of the fragments' sample counts
+    float* out;
+    const float* wss_per;
+    const double* w2;
+};
+
+__global__ void gl_extract_kernel(const GlExtractParams P) {
+    const int b = blockIdx.y;
+    const int t0 = P.t0[b], Tg = P.Tg[b];
+    const long long n_a = t0 == 0 ? 0 : (long long)HOP * t0 - (HALF - WIN_LPAD);
+    const long long cnt = P.raw_off[b + 1] - P.raw_off[b];
+    const float* src = P.ola + P.pad_off[b] - (long long)HOP * t0;         // indexed by the utterance's padded position
+    float* dst = P.out + P.raw_off[b];
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < cnt; i += (long long)gridDim.x * blockDim.x) {
+        const long long q = n_a + i + HALF;
+        float y = src[q];
+        const float w = wss_at((int)q, Tg, P.wss_per, P.w2);
+        if (w > FLT_MIN) y = y / w;
+        dst[i] = y;
+    }
+}
+
 }  // namespace unast

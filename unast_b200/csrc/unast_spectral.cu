@@ -106,64 +106,98 @@ struct unast_ctx {
     MelItems items{};
     float4* it_w = nullptr; int* it_k0 = nullptr; int2* it_mel = nullptr;
     int* d_err = nullptr;
+    int* d_abort = nullptr;
     std::vector<float> mel_basis;
 };
 
 // ---- diagnostics kernels ----------------------------------------------------------------------
 namespace unast {
 
-template <class T>
-__global__ void __launch_bounds__(128) debug_rfft_kernel(const float* __restrict__ frames, int F, const cplx_t<T>* tw,
-                                                         const cplx_t<T>* wp, float2* __restrict__ out) {
-    using C = cplx_t<T>;
+// The transform cores exactly as the product kernels run them, one frame per warp:
+//   float64: warp_fft1024_split + rfft_post_pairs (frontend_au_kernel<double>)
+//   float32: warp_fft1024_pk + pk_post_pairs / pk_pre_pairs + warp_fft1024_pk_b (gl_persist_kernel)
+__global__ void __launch_bounds__(128) debug_rfft_f64_kernel(const float* __restrict__ frames, int F, const double2* tw,
+                                                             const double2* wp, float2* __restrict__ out) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    C* xch = reinterpret_cast<C*>(smem) + warp * xch_elems<T>();
+    double* xs = reinterpret_cast<double*>(smem + warp * xs_bytes<double>());
     const int f = blockIdx.x * 4 + warp;
     if (f >= F) return;
     const float2* src = reinterpret_cast<const float2*>(frames + (size_t)f * NFFT);
-    C v[32];
+    double2 v[32];
     static_for<0, 18>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
         const int n = lane + 32 * j;
-        if (j < 17 || n < NLIVE_C) { float2 s = src[n]; v[j] = mk((T)0.5 * (T)s.x, (T)0.5 * (T)s.y); } else v[j] = mk((T)0, (T)0);
+        if (j < 17 || n < NLIVE_C) { const float2 q = src[n]; v[j] = mk(0.5 * (double)q.x, 0.5 * (double)q.y); } else v[j] = mk(0.0, 0.0);
     });
-    T nyq;
-    if constexpr (sizeof(T) == 4) {          // float: the low-shared-memory core the Griffin-Lim kernel uses
-        warp_fft1024_split<T, 18>(v, reinterpret_cast<T*>(xch), tw, lane);
-        rfft_post_shfl<T>(v, nyq, reinterpret_cast<C*>(reinterpret_cast<unsigned char*>(xch) + xs_bytes<T>()), WpTable<T>{wp}, lane);
-        nyq = __shfl_sync(0xffffffffu, nyq, 0);
-    } else {                                 // double: the core of the front-end kernel
-        warp_fft1024<T, 18>(v, xch, tw, lane);
-        rfft_post<T>(v, nyq, xch, WpTable<T>{wp}, lane);
-    }
+    static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = mk(0.0, 0.0); });
+    warp_fft1024_split<double, 18>(v, xs, tw, lane);
     float2* dst = out + (size_t)f * NBINS;
-    static_for<0, 32>([&](auto jj) {
+    rfft_post_pairs<double>(v, reinterpret_cast<double2*>(xs), WpLane<double>{wp[lane]}, lane, [&](auto jj, double2 xa, double2 xb) {
         constexpr int j = decltype(jj)::value;
-        dst[lane + 32 * j] = make_float2((float)v[j].x, (float)v[j].y);
-    });
-    if (lane == 0) dst[1024] = make_float2((float)nyq, 0.f);
+        dst[lane + 32 * j] = make_float2((float)xa.x, (float)xa.y);
+        dst[1024 - lane - 32 * j] = make_float2((float)xb.x, (float)xb.y);
+    }, [&](double2 x) { dst[512] = make_float2((float)x.x, (float)x.y); });
 }
 
-__global__ void __launch_bounds__(128) debug_irfft_kernel(const float2* __restrict__ spec, int F, const float2* tw,
-                                                          const float2* wp, float* __restrict__ out) {
+__global__ void __launch_bounds__(128) debug_rfft_pk_kernel(const float* __restrict__ frames, int F, const float4* tw4,
+                                                            const float4* wp4, float2* __restrict__ out) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float2* xch = reinterpret_cast<float2*>(smem) + warp * xch_elems<float>();
+    float* xs = reinterpret_cast<float*>(smem + warp * GLP_XS_BYTES);
+    const int f = blockIdx.x * 4 + warp;
+    if (f >= F) return;
+    const float2* src = reinterpret_cast<const float2*>(frames + (size_t)f * NFFT);
+    Pk v;
+    static_for<0, 18>([&](auto jj) {
+        constexpr int j = decltype(jj)::value;
+        const int n = lane + 32 * j;
+        if (j < 17 || n < NLIVE_C) { const float2 q = src[n]; reA<j>(v) = 0.5f * q.x; imA<j>(v) = 0.5f * q.y; } else { reA<j>(v) = 0.f; imA<j>(v) = 0.f; }
+    });
+    static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; reA<j>(v) = 0.f; imA<j>(v) = 0.f; });
+    warp_fft1024_pk<18>(v, xs, tw4, lane);
+    pk_post_pairs(v, xs, wp4, lane);
+    float2* dst = out + (size_t)f * NBINS;
+    static_for<0, 8>([&](auto mm) {
+        constexpr int m = decltype(mm)::value;
+        const int ka = lane + 64 * m;
+        dst[ka] = make_float2(v.re[m].x, v.im[m].x);
+        dst[ka + 32] = make_float2(v.re[m].y, v.im[m].y);
+        dst[1024 - ka] = make_float2(v.re[m + 8].x, v.im[m + 8].x);
+        dst[992 - ka] = make_float2(v.re[m + 8].y, v.im[m + 8].y);
+    });
+    if (lane == 0) dst[512] = make_float2(2.0f * xs[32 * PK_PARK_S + 16], -2.0f * xs[PK_PARK_PLANE + 32 * PK_PARK_S + 16]);
+}
+
+__global__ void __launch_bounds__(128) debug_irfft_kernel(const float2* __restrict__ spec, int F, const float4* tw4a,
+                                                          const float4* wp4, float* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* xs = reinterpret_cast<float*>(smem + warp * GLP_XS_BYTES);
     const int f = blockIdx.x * 4 + warp;
     if (f >= F) return;
     const float2* src = spec + (size_t)f * NBINS;
-    float2 v[32];
-    static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = src[lane + 32 * j]; });
-    if (lane == 0) v[0].y = 0.f;
-    float nyq = src[1024].x;
-    irfft_pre_shfl<float>(v, nyq, reinterpret_cast<float2*>(reinterpret_cast<unsigned char*>(xch) + xs_bytes<float>()), WpTable<float>{wp}, lane);
-    warp_fft1024_split<float, 32>(v, reinterpret_cast<float*>(xch), tw, lane);
+    Pk v;
+    static_for<0, 8>([&](auto mm) {
+        constexpr int m = decltype(mm)::value;
+        const int ka = lane + 64 * m;
+        const float2 a = src[ka], b = src[ka + 32], c = src[1024 - ka], d = src[992 - ka];
+        v.re[m] = make_float2(a.x, b.x); v.im[m] = make_float2(a.y, b.y);
+        v.re[m + 8] = make_float2(c.x, d.x); v.im[m + 8] = make_float2(c.y, d.y);
+    });
+    float2 x512 = make_float2(0.f, 0.f);
+    if (lane == 0) { v.im[0].x = 0.f; v.im[8].x = 0.f; x512 = src[512]; }      // irfft ignores Im of DC and Nyquist
+    pk_pre_pairs(v, xs, wp4, lane);
+    if (lane == 0) { xs[0] = 2.0f * x512.x; xs[PK_PARK_PLANE] = 2.0f * x512.y; }
+    __syncwarp();
+    pk_pre_collect(v, xs, lane);
+    __syncwarp();
+    warp_fft1024_pk_b(v, xs, tw4a, lane, []() {});
     float2* dst = reinterpret_cast<float2*>(out + (size_t)f * WIN);
     static_for<0, 18>([&](auto jj) {
         constexpr int j = decltype(jj)::value;
         const int n = lane + 32 * j;
-        if (j < 17 || n < NLIVE_C) dst[n] = make_float2(v[j].x * (1.0f / 2048.0f), -v[j].y * (1.0f / 2048.0f));
+        if (j < 17 || n < NLIVE_C) dst[n] = make_float2(reB<j>(v) * (1.0f / 2048.0f), -imB<j>(v) * (1.0f / 2048.0f));
     });
 }
 
@@ -349,12 +383,13 @@ int unast_create(int device, unast_ctx** out) {
     up(&c->wss_per, wss_per); up(&c->w2, w2);
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_err, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_abort, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(c->d_abort, 0, sizeof(int));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<float, FE32_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<float, FE32_WARPS>::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, FE64_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, FE64_WARPS>::bytes);
     c->items.w = c->it_w; c->items.k0 = c->it_k0; c->items.mel = c->it_mel;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_pk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_pk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(debug_rfft_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * xch_elems<double>() * 16);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
     *out = c;
     return UNAST_OK;
@@ -368,7 +403,7 @@ int unast_destroy(unast_ctx* c) {
     cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f);
     cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
     cudaFree(c->it_w); cudaFree(c->it_k0); cudaFree(c->it_mel);
-    cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->d_err);
+    cudaFree(c->wss_per); cudaFree(c->w2); cudaFree(c->d_err); cudaFree(c->d_abort);
     delete c;
     return UNAST_OK;
 }
@@ -386,6 +421,7 @@ int unast_check(unast_ctx* c, void* stream) {
         CU(cudaMemsetAsync(c->d_err, 0, sizeof(int), (cudaStream_t)stream));
         if (h == ERR_TOO_SHORT) return fail(UNAST_E_DATA, "an utterance is too short for reflect padding (needs > 1024 samples / >= 5 frames)");
         if (h == ERR_EMPTY) return fail(UNAST_E_DATA, "an utterance is empty after trimming");
+        if (h == ERR_SYNC) return fail(UNAST_E_DATA, "Griffin-Lim: a wait for a neighbouring run / peer rank timed out");
         return fail(UNAST_E_DATA, "kernel reported data error " + std::to_string(h));
     }
     return UNAST_OK;
@@ -466,43 +502,216 @@ int unast_frontend(unast_ctx* c, const void* wave, int dtype, const int64_t* wav
 // ---- Griffin-Lim ----
 namespace {
 constexpr int GL_MAX_RUNS = 8192;                                  // >= SMs x GL_WARPS: one run of frames per warp
+constexpr int GL_MIN_RUN = 9;                                      // frames: reflect reads and seams then reach only the adjacent run
+
+// A fragment is a contiguous range [t0, t0 + n) of the frames of an utterance of Tg frames.  Whole utterances are
+// fragments with t0 = 0, n = Tg; the sharded long-form run hands every rank one fragment of the waveform.
 struct GlPlan {
-    std::vector<int> frame_off;
-    std::vector<long long> pad_off, wav_off, cost_off;
-    long long total_frames = 0, total_pad = 0, total_wav = 0;
-    int max_wav = 0;
-    size_t o_runs = 0, o_meta_i = 0, o_meta_l = 0, o_S = 0, o_ola = 0, o_tprev = 0, o_be = 0, bytes = 0;
+    std::vector<int> frame_off, t0, Tg;
+    std::vector<long long> pad_off, cost_off;
+    long long total_frames = 0, total_pad = 0;
+    size_t o_runs = 0, o_meta_i = 0, o_meta_l = 0, o_sync = 0, o_mail = 0, o_S = 0, o_ola = 0, ola_stride = 0, o_tprev = 0, o_be = 0, bytes = 0;
 };
-bool gl_plan(const int32_t* frames, int B, float momentum, GlPlan& p) {
-    p.frame_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.wav_off.assign(B + 1, 0); p.cost_off.assign(B + 1, 0);
+// edge frames (reflect padding, envelope tables) cost 5, interior frames 4
+void frag_edges(int t0, int n, int Tg, int& head, int& tail) {
+    head = std::max(0, std::min(t0 + n, 4) - t0);
+    tail = std::max(0, t0 + n - std::max(t0, Tg - 4));
+    if (head + tail > n) tail = n - head;
+}
+bool gl_plan(const int32_t* frames, const int32_t* t0, const int32_t* tglob, int B, float momentum, int max_wav, GlPlan& p) {
+    p.frame_off.assign(B + 1, 0); p.pad_off.assign(B + 1, 0); p.cost_off.assign(B + 1, 0); p.t0.assign(B, 0); p.Tg.assign(B, 0);
     for (int b = 0; b < B; ++b) {
-        const int T = frames[b];
-        if (T < 5) return false;                                    // reflect padding of the in-loop stft needs 275 (T-1) > 1024
-        p.frame_off[b + 1] = p.frame_off[b] + T;
-        p.pad_off[b + 1] = p.pad_off[b] + NFFT + (long long)HOP * (T - 1);
-        p.wav_off[b + 1] = p.wav_off[b] + (long long)HOP * (T - 1);
-        p.cost_off[b + 1] = p.cost_off[b] + 4LL * T + std::min(T, 8);          // interior frame 4, edge frame 5 (gl_kernel)
-        p.max_wav = std::max(p.max_wav, HOP * (T - 1));
+        const int n = frames[b];
+        p.t0[b] = t0 ? t0[b] : 0;
+        p.Tg[b] = tglob ? tglob[b] : n;
+        if (p.Tg[b] < 5 || n < 1 || p.t0[b] < 0 || p.t0[b] + n > p.Tg[b]) return false;   // reflect padding needs 275 (T-1) > 1024
+        if (n != p.Tg[b] && n < GL_MIN_RUN) return false;           // a fragment must hold a whole run
+        int head, tail;
+        frag_edges(p.t0[b], n, p.Tg[b], head, tail);
+        p.frame_off[b + 1] = p.frame_off[b] + n;
+        p.pad_off[b + 1] = p.pad_off[b] + NFFT + (long long)HOP * (n - 1);
+        p.cost_off[b + 1] = p.cost_off[b] + 4LL * n + head + tail;
     }
-    p.total_frames = p.frame_off[B]; p.total_pad = p.pad_off[B]; p.total_wav = p.wav_off[B];
+    p.total_frames = p.frame_off[B]; p.total_pad = p.pad_off[B];
     size_t o = 0;
     p.o_runs = o; o += align256((size_t)GL_MAX_RUNS * sizeof(int4));
-    p.o_meta_i = o; o += align256(2 * (size_t)(B + 1) * sizeof(int));
-    p.o_meta_l = o; o += align256(3 * (size_t)(B + 1) * sizeof(long long));
+    p.o_meta_i = o; o += align256(3 * (size_t)(B + 1) * sizeof(int));
+    p.o_meta_l = o; o += align256(2 * (size_t)(B + 1) * sizeof(long long));
+    p.o_sync = o; o += align256((size_t)GL_MAX_RUNS * sizeof(int));
+    p.o_mail = o; o += align256((size_t)GL_MAX_LINKS * sizeof(int));
     p.o_S = o; o += align256((size_t)p.total_frames * S_STRIDE * sizeof(float));
-    p.o_ola = o; o += 3 * align256((size_t)p.total_pad * sizeof(float));
+    p.ola_stride = align256((size_t)p.total_pad * sizeof(float));
+    p.o_ola = o; o += 3 * p.ola_stride;
     p.o_tprev = o; if (momentum != 0.f) o += align256((size_t)p.total_frames * NBINS * sizeof(float2));
-    p.o_be = o; o += align256((size_t)B * nblk_of(p.max_wav) * sizeof(double));
+    p.o_be = o; o += align256((size_t)B * ((max_wav + TRIM_HOP - 1) / TRIM_HOP) * sizeof(double));
     p.bytes = o;
     return true;
+}
+int max_wav_of(const int32_t* frames, int B) {
+    int m = 0;
+    for (int b = 0; b < B; ++b) m = std::max(m, HOP * (frames[b] - 1));
+    return m;
+}
+
+// the frame at cost point cpt (costs as in gl_plan)
+int frame_at(const GlPlan& p, int B, long long cpt) {
+    if (cpt <= 0) return 0;
+    if (cpt >= p.cost_off[B]) return (int)p.total_frames;
+    int lo = 0, hi = B;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (p.cost_off[mid] <= cpt) lo = mid; else hi = mid; }
+    const int n = p.frame_off[lo + 1] - p.frame_off[lo];
+    int head, tail;
+    frag_edges(p.t0[lo], n, p.Tg[lo], head, tail);
+    const long long ci = cpt - p.cost_off[lo];
+    const long long inner = 4LL * (n - head - tail);
+    long long j;
+    if (ci < 5LL * head) j = ci / 5;
+    else if (ci < 5LL * head + inner) j = head + (ci - 5LL * head) / 4;
+    else j = n - tail + (ci - 5LL * head - inner) / 5;
+    return p.frame_off[lo] + (int)std::min<long long>(j, n - 1);
 }
 }  // namespace
 
 size_t unast_griffinlim_workspace_bytes(const int32_t* frames_host, int B, float momentum) {
     GlPlan p;
-    if (!frames_host || B <= 0 || !gl_plan(frames_host, B, momentum, p)) return 0;
+    if (!frames_host || B <= 0 || !gl_plan(frames_host, nullptr, nullptr, B, momentum, max_wav_of(frames_host, B), p)) return 0;
     return p.bytes;
 }
+
+int unast_griffinlim_layout(const int32_t* frames_host, int B, float momentum, size_t* out5) {
+    GlPlan p;
+    if (!frames_host || !out5 || B <= 0) return fail(UNAST_E_ARG, "unast_griffinlim_layout: bad argument");
+    std::vector<int32_t> big(B);
+    for (int b = 0; b < B; ++b) big[b] = frames_host[b] + 2 * GL_MIN_RUN;     // any valid (t0, Tg): the layout depends on n only
+    if (!gl_plan(frames_host, nullptr, big.data(), B, momentum, max_wav_of(frames_host, B), p)) return fail(UNAST_E_ARG, "unast_griffinlim_layout: bad frame counts");
+    out5[0] = p.o_ola; out5[1] = p.o_ola + p.ola_stride; out5[2] = p.o_ola + 2 * p.ola_stride; out5[3] = p.o_mail; out5[4] = p.bytes;
+    return UNAST_OK;
+}
+
+namespace {
+struct GlDev {                      // device views of one call's workspace
+    int* frame_off; int* t0; int* Tg; long long* pad_off; long long* aux_off; float* ola[3]; int final_buf; double* be;
+};
+
+// Everything up to and including the persistent launch; shared by the whole-utterance and the fragment entry points.
+int gl_run(unast_ctx* c, const float* mag_norm, const GlPlan& p, int B, const unast_gl_link* links, int n_links, int epoch, int n_iter,
+           float momentum, const float* angles0, float power, char* ws, cudaStream_t st, GlDev& d) {
+    d.frame_off = (int*)(ws + p.o_meta_i);
+    d.t0 = d.frame_off + (B + 1);
+    d.Tg = d.t0 + (B + 1);
+    d.pad_off = (long long*)(ws + p.o_meta_l);
+    d.aux_off = d.pad_off + (B + 1);
+    d.be = (double*)(ws + p.o_be);
+    CU(cudaMemcpyAsync(d.frame_off, p.frame_off.data(), (B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d.t0, p.t0.data(), B * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d.Tg, p.Tg.data(), B * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d.pad_off, p.pad_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    float* S = (float*)(ws + p.o_S);
+    for (int k = 0; k < 3; ++k) d.ola[k] = (float*)(ws + p.o_ola + k * p.ola_stride);
+    d.final_buf = (n_iter + 1) % 3;
+    CU(cudaMemsetAsync(d.ola[0], 0, 3 * p.ola_stride, st));
+    CU(cudaMemsetAsync(ws + p.o_sync, 0, (size_t)GL_MAX_RUNS * sizeof(int), st));
+    CU(cudaMemsetAsync(c->d_abort, 0, sizeof(int), st));
+    gl_prepare_kernel<<<c->num_sms * 8, 256, 0, st>>>(mag_norm, p.total_frames, power, S);
+
+    GlParams P;
+    memset(&P, 0, sizeof(P));
+    P.S = S; P.frame_off = d.frame_off; P.pad_off = d.pad_off; P.t0 = d.t0; P.Tg = d.Tg; P.B = B;
+    for (int k = 0; k < 3; ++k) P.ola[k] = d.ola[k];
+    P.n_iter = n_iter; P.done = (int*)(ws + p.o_sync); P.epoch = epoch; P.abort = c->d_abort; P.err = c->d_err;
+    P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
+    P.angles0 = (const float2*)angles0;
+    P.alpha = momentum / (1.0f + momentum);
+    P.wa2 = c->wa2_f; P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw4 = c->tw4_f; P.tw4a = c->tw4a_f; P.wp4 = c->wp4_f; P.phi = c->phi_f;
+    P.rinv_l = c->rinv_l; P.rinv_r = c->rinv_r; P.wss_per = c->wss_per; P.w2 = c->w2;
+
+    // ---- segments: linked seams cut the frame list; a run never spans one ----
+    if (n_links < 0 || n_links > GL_MAX_LINKS) return fail(UNAST_E_ARG, "unast_griffinlim: too many links");
+    std::vector<int> cut(1, 0);                                        // frame indices where a segment starts
+    std::vector<int> link_at_start(B + 1, -1), link_at_end(B + 1, -1); // link index by fragment
+    int* mail = (int*)(ws + p.o_mail);
+    for (int i = 0; i < n_links; ++i) {
+        const unast_gl_link& L = links[i];
+        if (L.fragment < 0 || L.fragment >= B || (L.side != 0 && L.side != 1) || L.my_mail < 0 || L.my_mail >= GL_MAX_LINKS || !L.peer_mail)
+            return fail(UNAST_E_ARG, "unast_griffinlim: bad link");
+        const int b = L.fragment, n = p.frame_off[b + 1] - p.frame_off[b];
+        long long seam0;                                               // local index of the seam's first sample
+        if (L.side == 0) {
+            if (p.t0[b] == 0 || link_at_start[b] >= 0) return fail(UNAST_E_ARG, "unast_griffinlim: left link on a fragment that starts its utterance");
+            link_at_start[b] = i; cut.push_back(p.frame_off[b]); seam0 = p.pad_off[b] + WIN_LPAD;
+        } else {
+            if (p.t0[b] + n == p.Tg[b] || link_at_end[b] >= 0) return fail(UNAST_E_ARG, "unast_griffinlim: right link on a fragment that ends its utterance");
+            link_at_end[b] = i; cut.push_back(p.frame_off[b + 1]); seam0 = p.pad_off[b] + (long long)HOP * n + WIN_LPAD;
+        }
+        for (int k = 0; k < 3; ++k) {
+            if (!L.peer_ola[k] || ((uintptr_t)L.peer_ola[k] & 3)) return fail(UNAST_E_ARG, "unast_griffinlim: bad peer buffer");
+            P.links[i].peer[k] = (float*)L.peer_ola[k] - seam0;
+        }
+        P.links[i].push = (int*)L.peer_mail;
+        P.links[i].poll = mail + L.my_mail;
+    }
+    cut.push_back((int)p.total_frames);
+    std::sort(cut.begin(), cut.end());
+    cut.erase(std::unique(cut.begin(), cut.end()), cut.end());
+
+    // ---- one run of frames per warp: equal shares of the cost inside every segment, runs of >= GL_MIN_RUN frames ----
+    const int Wmax = std::min(GL_MAX_RUNS, c->num_sms * GL_WARPS);
+    const int nseg = (int)cut.size() - 1;
+    if (nseg > Wmax) return fail(UNAST_E_ARG, "unast_griffinlim: more segments than warps");
+    auto cost_of_frame_index = [&](int f) -> long long {              // cost prefix at frame f
+        if (f >= p.total_frames) return p.cost_off[B];
+        int lo = 0, hi = B;
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (p.frame_off[mid] <= f) lo = mid; else hi = mid; }
+        const int n = p.frame_off[lo + 1] - p.frame_off[lo], j = f - p.frame_off[lo];
+        int head, tail;
+        frag_edges(p.t0[lo], n, p.Tg[lo], head, tail);
+        return p.cost_off[lo] + 4LL * j + std::min(j, head) + std::max(0, j - (n - tail));
+    };
+    std::vector<int> wseg(nseg);
+    int wsum = 0;
+    for (int s = 0; s < nseg; ++s) {
+        const long long cs = cost_of_frame_index(cut[s + 1]) - cost_of_frame_index(cut[s]);
+        const int frames_s = cut[s + 1] - cut[s];
+        long long w = (long long)Wmax * cs / std::max<long long>(1, p.cost_off[B]);
+        w = std::min<long long>(w, frames_s / GL_MIN_RUN);
+        wseg[s] = (int)std::max<long long>(1, w);
+        wsum += wseg[s];
+    }
+    while (wsum > Wmax) { int big = 0; for (int s = 1; s < nseg; ++s) if (wseg[s] > wseg[big]) big = s; --wseg[big]; --wsum; }
+    std::vector<int4> runs;
+    runs.reserve(wsum);
+    int b = 0;
+    for (int s = 0; s < nseg; ++s) {
+        const long long c0 = cost_of_frame_index(cut[s]), c1 = cost_of_frame_index(cut[s + 1]);
+        int prev = cut[s];
+        for (int i = 0; i < wseg[s]; ++i) {
+            int f1 = i + 1 == wseg[s] ? cut[s + 1] : frame_at(p, B, c0 + (c1 - c0) * (i + 1) / wseg[s]);
+            f1 = std::max(f1, prev + 1);
+            f1 = std::min(f1, cut[s + 1] - (wseg[s] - 1 - i));
+            while (b + 1 < B && p.frame_off[b + 1] <= prev) ++b;
+            int ll = -1, lr = -1;
+            if (i == 0 && prev == p.frame_off[b]) ll = link_at_start[b];
+            if (i + 1 == wseg[s]) {                                       // the fragment this run ends in
+                int be = b;
+                while (be + 1 < B && p.frame_off[be + 1] < f1) ++be;
+                if (f1 == p.frame_off[be + 1]) lr = link_at_end[be];
+            }
+            runs.push_back(make_int4(prev, f1, b, (ll + 1) | ((lr + 1) << 16)));
+            prev = f1;
+        }
+    }
+    P.n_runs = (int)runs.size();
+    P.runs = (const int4*)(ws + p.o_runs);
+    CU(cudaMemcpyAsync(ws + p.o_runs, runs.data(), runs.size() * sizeof(int4), cudaMemcpyHostToDevice, st));
+
+    // one cooperative launch: every CTA must be resident, warps wait for one another
+    const int grid = (P.n_runs + GL_WARPS - 1) / GL_WARPS;
+    void* args[] = {(void*)&P};
+    const void* fn = momentum != 0.f ? (const void*)gl_persist_kernel<true> : (const void*)gl_persist_kernel<false>;
+    CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(GL_WARPS * 32), args, (size_t)glp_smem_bytes, st));
+    return UNAST_OK;
+}
+}  // namespace
 
 int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_host, int B, int n_iter, float momentum,
                      const float* angles0, float power, int deemphasis, float* wav_out, int32_t* bounds_out,
@@ -510,97 +719,143 @@ int unast_griffinlim(unast_ctx* c, const float* mag_norm, const int32_t* frames_
     if (!c || !mag_norm || !frames_host || !wav_out || B <= 0 || n_iter < 0) return fail(UNAST_E_ARG, "unast_griffinlim: bad argument");
     if (momentum < 0.f || momentum >= 1.f) return fail(UNAST_E_ARG, "unast_griffinlim: momentum must be in [0, 1)");
     GlPlan p;
-    if (!gl_plan(frames_host, B, momentum, p)) return fail(UNAST_E_ARG, "unast_griffinlim: every utterance needs >= 5 frames (librosa reflect padding)");
+    const int max_wav = max_wav_of(frames_host, B);
+    if (!gl_plan(frames_host, nullptr, nullptr, B, momentum, max_wav, p)) return fail(UNAST_E_ARG, "unast_griffinlim: every utterance needs >= 5 frames (librosa reflect padding)");
     if (!workspace || workspace_bytes < p.bytes) return fail(UNAST_E_WORKSPACE, "unast_griffinlim: workspace too small");
     DeviceGuard guard(c->device);
     if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     cudaStream_t st = (cudaStream_t)stream;
     char* ws = (char*)workspace;
-    int* d_frame_off = (int*)(ws + p.o_meta_i);
-    long long* d_pad_off = (long long*)(ws + p.o_meta_l);
-    long long* d_wav_off = d_pad_off + (B + 1);
-    long long* d_cost_off = d_wav_off + (B + 1);
-    CU(cudaMemcpyAsync(d_frame_off, p.frame_off.data(), (B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(d_pad_off, p.pad_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(d_wav_off, p.wav_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(d_cost_off, p.cost_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
-    float* S = (float*)(ws + p.o_S);
-    const size_t ola_stride = align256((size_t)p.total_pad * sizeof(float));
-    float* ola[3] = {(float*)(ws + p.o_ola), (float*)(ws + p.o_ola + ola_stride), (float*)(ws + p.o_ola + 2 * ola_stride)};
-    CU(cudaMemsetAsync(ola[0], 0, 3 * ola_stride, st));
-    gl_prepare_kernel<<<c->num_sms * 8, 256, 0, st>>>(mag_norm, p.total_frames, power, S);
-
-    GlParams P;
-    P.S = S; P.frame_off = d_frame_off; P.pad_off = d_pad_off; P.B = B; P.total_frames = (int)p.total_frames; P.cost_off = d_cost_off;
-    P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
-    P.angles0 = (const float2*)angles0;
-    P.alpha = momentum / (1.0f + momentum);
-    P.wa2 = c->wa2_f; P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw1024 = c->tw_f; P.tw4 = c->tw4_f; P.tw4a = c->tw4a_f; P.wp4 = c->wp4_f; P.wp2 = c->wp_f; P.phi = c->phi_f;
-    P.rinv_l = c->rinv_l; P.rinv_r = c->rinv_r; P.wss_per = c->wss_per; P.w2 = c->w2;
-    // one run of frames per warp; keep runs >= 8 frames so that seams (atomics) stay a small share
-    const int grid = (int)std::max<long long>(1, std::min<long long>(c->num_sms, p.total_frames / (8 * GL_WARPS)));
-    // The run partition is the same for every iteration: resolve it once on the host (equal shares of the cost that
-    // weights edge frames 5 : 4; see GlPlan::cost_off) instead of by dependent global loads at every launch.
-    {
-        const long long W = (long long)grid * GL_WARPS, total_cost = p.cost_off[B];
-        if (W > GL_MAX_RUNS) return fail(UNAST_E_ARG, "unast_griffinlim: too many SMs for the run table");
-        auto frame_at = [&](long long cpt) -> int {
-            if (cpt <= 0) return 0;
-            if (cpt >= total_cost) return (int)p.total_frames;
-            int lo = 0, hi = B;
-            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (p.cost_off[mid] <= cpt) lo = mid; else hi = mid; }
-            const int T = p.frame_off[lo + 1] - p.frame_off[lo];
-            const int ci = (int)(cpt - p.cost_off[lo]), head = 5 * std::min(4, T), inner = 4 * std::max(0, T - 8);
-            int t;
-            if (ci < head) t = ci / 5;
-            else if (ci < head + inner) t = 4 + (ci - head) / 4;
-            else t = 4 + std::max(0, T - 8) + (ci - head - inner) / 5;
-            return p.frame_off[lo] + std::min(t, T - 1);
-        };
-        std::vector<int4> runs((size_t)W);
-        int b = 0;
-        for (long long w = 0; w < W; ++w) {
-            const int f0 = frame_at(total_cost * w / W), f1 = frame_at(total_cost * (w + 1) / W);
-            while (b + 1 < B && p.frame_off[b + 1] <= f0) ++b;
-            runs[(size_t)w] = make_int4(f0, f1, b, 0);
-        }
-        CU(cudaMemcpyAsync(ws + p.o_runs, runs.data(), (size_t)W * sizeof(int4), cudaMemcpyHostToDevice, st));
-        P.runs = (const int4*)(ws + p.o_runs);
-    }
-    cudaError_t launch_err = cudaSuccess;
-    auto launch = [&]() {
-        // programmatic dependent launch (see the kernel's prologue)
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GL_WARPS * 32); cfg.dynamicSmemBytes = glp_smem_bytes; cfg.stream = st;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = at; cfg.numAttrs = 1;
-        const cudaError_t e = momentum != 0.f ? cudaLaunchKernelEx(&cfg, gl_pk_kernel<true>, P) : cudaLaunchKernelEx(&cfg, gl_pk_kernel<false>, P);
-        if (launch_err == cudaSuccess) launch_err = e;
-    };
-    P.mode = GL_INIT; P.first_iter = 1; P.ola_r = nullptr; P.ola_w = ola[1]; P.ola_z = ola[2];
-    launch();
-    for (int it = 1; it <= n_iter; ++it) {
-        P.mode = GL_ITER; P.first_iter = it == 1;
-        P.ola_r = ola[it % 3]; P.ola_w = ola[(it + 1) % 3]; P.ola_z = ola[(it + 2) % 3];
-        launch();
-    }
-    CU(launch_err);
-    CU(cudaGetLastError());
+    GlDev d;
+    const int rc = gl_run(c, mag_norm, p, B, nullptr, 0, 1, n_iter, momentum, angles0, power, ws, st, d);
+    if (rc != UNAST_OK) return rc;
+    std::vector<long long> wav_off(B + 1, 0);
+    for (int b = 0; b < B; ++b) wav_off[b + 1] = wav_off[b] + (long long)HOP * (frames_host[b] - 1);
+    CU(cudaMemcpyAsync(d.aux_off, wav_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
 
     DeemphParams D;
-    D.ola = ola[(n_iter + 1) % 3]; D.x = nullptr; D.frame_off = d_frame_off; D.pad_off = d_pad_off; D.wav_off = d_wav_off;
+    D.ola = d.ola[d.final_buf]; D.x = nullptr; D.frame_off = d.frame_off; D.pad_off = d.pad_off; D.wav_off = d.aux_off;
     D.out = wav_out; D.wss_per = c->wss_per; D.w2 = c->w2; D.coef = deemphasis ? 0.97 : 0.0;
-    const int chunks = (p.max_wav + DE_CHUNK - 1) / DE_CHUNK;
+    const int chunks = (max_wav + DE_CHUNK - 1) / DE_CHUNK;
     deemph_kernel<<<dim3((chunks + 3) / 4, B), 128, 0, st>>>(D);
     if (bounds_out) {
-        const int nblk = nblk_of(p.max_wav);
-        double* be = (double*)(ws + p.o_be);
-        block_energy_kernel<<<dim3((nblk + 7) / 8, B), 256, 0, st>>>(wav_out, 0, d_wav_off, B, nblk, be);
-        trim_decide_kernel<<<B, 128, 0, st>>>(wav_out, 0, d_wav_off, nblk, be, bounds_out, c->d_err);
+        const int nblk = nblk_of(max_wav);
+        block_energy_kernel<<<dim3((nblk + 7) / 8, B), 256, 0, st>>>(wav_out, 0, d.aux_off, B, nblk, d.be);
+        trim_decide_kernel<<<B, 128, 0, st>>>(wav_out, 0, d.aux_off, nblk, d.be, bounds_out, c->d_err);
     }
     CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+// samples of the whole utterance's waveform a fragment owns: [275 t0 - 551, 275 (t0 + n) - 551), clipped to [0, 275 (Tg - 1))
+static void frag_samples(int t0, int n, int Tg, long long& a, long long& b) {
+    a = t0 == 0 ? 0 : (long long)HOP * t0 - (HALF - WIN_LPAD);
+    b = t0 + n == Tg ? (long long)HOP * (Tg - 1) : (long long)HOP * (t0 + n) - (HALF - WIN_LPAD);
+}
+
+int unast_griffinlim_fragment_samples(int32_t t0, int32_t n, int32_t tglob, int64_t* first_out, int64_t* end_out) {
+    if (!first_out || !end_out || n < 1 || t0 < 0 || t0 + n > tglob) return fail(UNAST_E_ARG, "unast_griffinlim_fragment_samples: bad argument");
+    long long a, b;
+    frag_samples(t0, n, tglob, a, b);
+    *first_out = a; *end_out = b;
+    return UNAST_OK;
+}
+
+int unast_griffinlim_fragments(unast_ctx* c, const float* mag_norm, const int32_t* frames_host, const int32_t* t0_host,
+                               const int32_t* tglob_host, int B, const unast_gl_link* links_host, int n_links, int epoch, int n_iter,
+                               float momentum, const float* angles0, float power, float* raw_out, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+    if (!c || !mag_norm || !frames_host || !t0_host || !tglob_host || !raw_out || B <= 0 || n_iter < 0 || epoch < 1)
+        return fail(UNAST_E_ARG, "unast_griffinlim_fragments: bad argument");
+    if (n_links > 0 && !links_host) return fail(UNAST_E_ARG, "unast_griffinlim_fragments: links is NULL");
+    if (momentum < 0.f || momentum >= 1.f) return fail(UNAST_E_ARG, "unast_griffinlim_fragments: momentum must be in [0, 1)");
+    GlPlan p;
+    if (!gl_plan(frames_host, t0_host, tglob_host, B, momentum, max_wav_of(frames_host, B), p))
+        return fail(UNAST_E_ARG, "unast_griffinlim_fragments: bad fragment (utterances need >= 5 frames, partial fragments >= 9)");
+    if (!workspace || workspace_bytes < p.bytes) return fail(UNAST_E_WORKSPACE, "unast_griffinlim_fragments: workspace too small");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)workspace;
+    GlDev d;
+    const int rc = gl_run(c, mag_norm, p, B, links_host, n_links, epoch, n_iter, momentum, angles0, power, ws, st, d);
+    if (rc != UNAST_OK) return rc;
+    std::vector<long long> raw_off(B + 1, 0);
+    long long longest = 0;
+    for (int b = 0; b < B; ++b) {
+        long long a, e;
+        frag_samples(p.t0[b], frames_host[b], p.Tg[b], a, e);
+        raw_off[b + 1] = raw_off[b] + (e - a);
+        longest = std::max(longest, e - a);
+    }
+    CU(cudaMemcpyAsync(d.aux_off, raw_off.data(), (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    GlExtractParams X;
+    X.ola = d.ola[d.final_buf]; X.frame_off = d.frame_off; X.pad_off = d.pad_off; X.t0 = d.t0; X.Tg = d.Tg; X.raw_off = d.aux_off;
+    X.out = raw_out; X.wss_per = c->wss_per; X.w2 = c->w2;
+    gl_extract_kernel<<<dim3((unsigned)std::min<long long>(4096, (longest + 1023) / 1024), B), 256, 0, st>>>(X);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+/* de-emphasis (float64 IIR, utils.py:301) + librosa.effects.trim bounds of plain, already normalised waveforms: the
+ * epilogue of the sharded run once the fragments' samples have been gathered */
+size_t unast_deemph_trim_workspace_bytes(int B, int max_len) { return unast_trim_workspace_bytes(B, max_len) + align256((size_t)(B + 1) * sizeof(long long)); }
+
+int unast_deemph_trim(unast_ctx* c, const float* x, const int64_t* off, int B, int max_len, int deemphasis, float* wav_out,
+                      int32_t* bounds_out, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!c || !x || !off || !wav_out || B <= 0 || max_len <= 0) return fail(UNAST_E_ARG, "unast_deemph_trim: bad argument");
+    if (!workspace || workspace_bytes < unast_deemph_trim_workspace_bytes(B, max_len)) return fail(UNAST_E_WORKSPACE, "unast_deemph_trim: workspace too small");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
+    cudaStream_t st = (cudaStream_t)stream;
+    DeemphParams D;
+    D.ola = nullptr; D.x = x; D.frame_off = nullptr; D.pad_off = nullptr; D.wav_off = (const long long*)off;
+    D.out = wav_out; D.wss_per = c->wss_per; D.w2 = c->w2; D.coef = deemphasis ? 0.97 : 0.0;
+    const int chunks = (max_len + DE_CHUNK - 1) / DE_CHUNK;
+    deemph_kernel<<<dim3((chunks + 3) / 4, B), 128, 0, st>>>(D);
+    if (bounds_out) {
+        const int nblk = nblk_of(max_len);
+        block_energy_kernel<<<dim3((nblk + 7) / 8, B), 256, 0, st>>>(wav_out, 0, (const long long*)off, B, nblk, (double*)workspace);
+        trim_decide_kernel<<<B, 128, 0, st>>>(wav_out, 0, (const long long*)off, nblk, (const double*)workspace, bounds_out, c->d_err);
+    }
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+/* ---- peer-shareable device memory (CUDA IPC) for the linked overlap-add buffers ---- */
+int unast_peer_alloc(unast_ctx* c, size_t bytes, void** dptr, unsigned char* handle64) {
+    if (!c || !dptr || !handle64 || bytes == 0) return fail(UNAST_E_ARG, "unast_peer_alloc: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
+    void* p = nullptr;
+    CU(cudaMalloc(&p, bytes));
+    CU(cudaMemset(p, 0, bytes));                                         // mailboxes start at zero; epochs only grow
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, p));
+    memcpy(handle64, &h, 64);
+    *dptr = p;
+    return UNAST_OK;
+}
+int unast_peer_open(unast_ctx* c, const unsigned char* handle64, void** dptr) {
+    if (!c || !dptr || !handle64) return fail(UNAST_E_ARG, "unast_peer_open: bad argument");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    CU(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return UNAST_OK;
+}
+int unast_peer_close(unast_ctx* c, void* dptr) {
+    if (!c || !dptr) return fail(UNAST_E_ARG, "unast_peer_close: bad argument");
+    DeviceGuard guard(c->device);
+    CU(cudaIpcCloseMemHandle(dptr));
+    return UNAST_OK;
+}
+int unast_peer_free(unast_ctx* c, void* dptr) {
+    if (!c || !dptr) return fail(UNAST_E_ARG, "unast_peer_free: bad argument");
+    DeviceGuard guard(c->device);
+    CU(cudaFree(dptr));
     return UNAST_OK;
 }
 
@@ -640,9 +895,9 @@ int unast_debug_rfft(unast_ctx* c, const float* frames, int F, int precision, fl
     if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
     cudaStream_t st = (cudaStream_t)stream;
     if (precision == UNAST_PREC_F64)
-        debug_rfft_kernel<double><<<(F + 3) / 4, 128, 4 * xch_elems<double>() * 16, st>>>(frames, F, c->tw_d, c->wp_d, (float2*)out);
+        debug_rfft_f64_kernel<<<(F + 3) / 4, 128, 4 * xs_bytes<double>(), st>>>(frames, F, c->tw_d, c->wp_d, (float2*)out);
     else
-        debug_rfft_kernel<float><<<(F + 3) / 4, 128, 4 * xch_elems<float>() * 8, st>>>(frames, F, c->tw_f, c->wp_f, (float2*)out);
+        debug_rfft_pk_kernel<<<(F + 3) / 4, 128, 4 * GLP_XS_BYTES, st>>>(frames, F, c->tw4_f, c->wp4_f, (float2*)out);
     CU(cudaGetLastError());
     return UNAST_OK;
 }
@@ -651,7 +906,7 @@ int unast_debug_irfft(unast_ctx* c, const float* spec, int F, float* out, void* 
     if (!c || !spec || !out || F <= 0) return fail(UNAST_E_ARG, "unast_debug_irfft: bad argument");
     DeviceGuard guard(c->device);
     if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
-    debug_irfft_kernel<<<(F + 3) / 4, 128, 4 * xch_elems<float>() * 8, (cudaStream_t)stream>>>((const float2*)spec, F, c->tw_f, c->wp_f, out);
+    debug_irfft_kernel<<<(F + 3) / 4, 128, 4 * GLP_XS_BYTES, (cudaStream_t)stream>>>((const float2*)spec, F, c->tw4a_f, c->wp4_f, out);
     CU(cudaGetLastError());
     return UNAST_OK;
 }

@@ -55,10 +55,10 @@ class SpectralEngine:
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
-    def _workspace(self, key, nbytes):
+    def _workspace(self, key, nbytes, zero=False):
         t = self._ws.get(key)
         if t is None or t.numel() < nbytes:
-            t = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=self.device)
+            t = (torch.zeros if zero else torch.empty)(max(int(nbytes), 256), dtype=torch.uint8, device=self.device)
             self._ws[key] = t
         return t
 
@@ -154,8 +154,96 @@ class SpectralEngine:
         bounds = torch.empty((B, 2), dtype=torch.int32, device=self.device) if want_trim else None
         L.check(self.lib.unast_griffinlim(self.h, _ptr(mag_norm), fptr, B, int(n_iter), float(momentum), _ptr(a0), float(power),
                                           1 if deemphasis else 0, _ptr(wav_out), _ptr(bounds), _ptr(ws), nbytes, self._stream()))
-        self.launches += 3 + int(n_iter) + (2 if want_trim else 0)
+        self.launches += 3 + (2 if want_trim else 0)        # prepare, ONE persistent Griffin-Lim launch, de-emphasis (+ trim)
         return wav_out, wav_off, bounds
+
+    # -- sharded long-form Griffin-Lim ------------------------------------------
+    def gl_layout(self, frames, momentum=0.0):
+        """Byte offsets (ola0, ola1, ola2, mailboxes, total) of a Griffin-Lim workspace for these fragment sizes."""
+        fr = np.ascontiguousarray(np.asarray(frames, dtype=np.int32))
+        out = (C.c_size_t * 5)()
+        L.check(self.lib.unast_griffinlim_layout(fr.ctypes.data_as(C.c_void_p), int(fr.size), float(momentum), C.cast(out, C.c_void_p)))
+        return [int(v) for v in out]
+
+    @staticmethod
+    def gl_pad_offsets(frames):
+        """pad_off of the C ABI: prefix sum of 2048 + 275 (n - 1) floats over the fragments."""
+        fr = np.asarray(frames, dtype=np.int64)
+        return np.concatenate([[0], np.cumsum(NFFT + HOP * (fr - 1))])
+
+    def fragment_samples(self, t0, n, tglob):
+        a, b = C.c_int64(), C.c_int64()
+        L.check(self.lib.unast_griffinlim_fragment_samples(int(t0), int(n), int(tglob), C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def griffinlim_fragments(self, mag_norm, frames, t0, tglob, links=(), epoch=1, n_iter=ap.n_iter, momentum=0.0, angles0=None,
+                             power=ap.power, workspace=None, raw_out=None):
+        """Griffin-Lim iterations on fragments [t0, t0 + n) of longer utterances; `links` = dicts with keys fragment, side,
+        peer_ola (3 addresses), peer_mail (address), my_mail (slot) -- see include/unast_spectral.h.  Returns
+        (raw float32 [sum owned samples], raw_off numpy int64 [B+1]): normalised, not de-emphasised."""
+        fr = np.ascontiguousarray(np.asarray(frames, dtype=np.int32))
+        t0a = np.ascontiguousarray(np.asarray(t0, dtype=np.int32))
+        tga = np.ascontiguousarray(np.asarray(tglob, dtype=np.int32))
+        B = int(fr.size)
+        if mag_norm.dtype != torch.float32 or not mag_norm.is_contiguous() or mag_norm.numel() != int(fr.sum()) * NBINS:
+            raise TypeError("mag_norm must be a contiguous float32 [sum n, 1025] tensor")
+        a0 = None
+        if angles0 is not None:
+            if angles0.dtype != torch.complex64 or not angles0.is_contiguous() or angles0.numel() != int(fr.sum()) * NBINS:
+                raise TypeError("angles0 must be a contiguous complex64 [sum n, 1025] tensor")
+            a0 = torch.view_as_real(angles0)
+        nbytes = self.lib.unast_griffinlim_workspace_bytes(fr.ctypes.data_as(C.c_void_p), B, float(momentum))
+        if nbytes == 0:
+            raise ValueError("bad fragment sizes")
+        if workspace is None:
+            ws_ptr = _ptr(self._workspace("glf", nbytes, zero=True))
+        else:
+            ws_ptr = C.c_void_p(int(workspace))
+        counts = [self.fragment_samples(a, n, t) for a, n, t in zip(t0a, fr, tga)]
+        raw_off = np.concatenate([[0], np.cumsum([e - s for s, e in counts])]).astype(np.int64)
+        if raw_out is None:
+            raw_out = torch.empty(int(raw_off[-1]), dtype=torch.float32, device=self.device)
+        arr = (L.GlLink * max(1, len(links)))()
+        for i, lk in enumerate(links):
+            arr[i].fragment, arr[i].side, arr[i].my_mail = int(lk["fragment"]), int(lk["side"]), int(lk["my_mail"])
+            for k in range(3):
+                arr[i].peer_ola[k] = int(lk["peer_ola"][k])
+            arr[i].peer_mail = int(lk["peer_mail"])
+        L.check(self.lib.unast_griffinlim_fragments(self.h, _ptr(mag_norm), fr.ctypes.data_as(C.c_void_p), t0a.ctypes.data_as(C.c_void_p),
+                                                    tga.ctypes.data_as(C.c_void_p), B, C.cast(arr, C.c_void_p), len(links), int(epoch),
+                                                    int(n_iter), float(momentum), _ptr(a0), float(power), _ptr(raw_out), ws_ptr, nbytes,
+                                                    self._stream()))
+        self.launches += 3
+        return raw_out, raw_off
+
+    def deemph_trim(self, x, offsets, max_len, deemphasis=True, want_trim=True):
+        """lfilter([1], [1, -0.97]) in float64 + librosa.effects.trim bounds of plain waveforms (device float32 / int64)."""
+        B = offsets.numel() - 1
+        out = torch.empty_like(x)
+        bounds = torch.empty((B, 2), dtype=torch.int32, device=self.device) if want_trim else None
+        nbytes = self.lib.unast_deemph_trim_workspace_bytes(B, int(max_len))
+        ws = self._workspace("det", nbytes)
+        L.check(self.lib.unast_deemph_trim(self.h, _ptr(x), _ptr(offsets), B, int(max_len), 1 if deemphasis else 0, _ptr(out), _ptr(bounds),
+                                           _ptr(ws), nbytes, self._stream()))
+        self.launches += 1 + (2 if want_trim else 0)
+        return out, bounds
+
+    def peer_alloc(self, nbytes):
+        """(device address, 64-byte IPC handle) of zero-filled device memory other processes of the node can map."""
+        p, h = C.c_void_p(), (C.c_ubyte * 64)()
+        L.check(self.lib.unast_peer_alloc(self.h, int(nbytes), C.byref(p), C.cast(h, C.c_void_p)))
+        return int(p.value), bytes(h)
+
+    def peer_open(self, handle):
+        p, h = C.c_void_p(), (C.c_ubyte * 64).from_buffer_copy(handle)
+        L.check(self.lib.unast_peer_open(self.h, C.cast(h, C.c_void_p), C.byref(p)))
+        return int(p.value)
+
+    def peer_close(self, addr):
+        L.check(self.lib.unast_peer_close(self.h, C.c_void_p(int(addr))))
+
+    def peer_free(self, addr):
+        L.check(self.lib.unast_peer_free(self.h, C.c_void_p(int(addr))))
 
     def mel_augment(self, x, spans=None, keep=None, replace_with_zero=False, out=None):
         """utils.py:40-75 on a float32 [B, T, D] device batch: row spans (int32 [B, 4] = f_zero, f, t_zero, t) filled

@@ -8,8 +8,14 @@ that starts `HALO` frames early and ends `HALO` frames late contains everything,
 real signal boundary -- are dropped.  Every kept frame goes through exactly the arithmetic of the single-GPU run
 (bit-identical, tests/test_gpu_parity.py); there is no exchange and no collective.
 
-The inverse (Griffin-Lim on one long waveform) would need a seam exchange per iteration and is run as replicas only
-(multi-GPU).  Reference semantics: src/utils.py:245-276 (`get_spectrograms`) on a long file.
+The inverse (Griffin-Lim on one long waveform, src/utils.py:309-320) is sharded the same way -- rank r owns a contiguous
+fragment of the frames -- but its iterations are coupled: the 827 samples that the last frames of one fragment share with
+the first frames of the next (a *linked seam*) exist in both ranks' overlap-add buffers, and every iteration both sides
+add their partial sums into both copies with stores / atomics over NVLink peer mappings (CUDA IPC) and publish their
+progress in the neighbour's mailbox.  One persistent kernel per rank and call, no collective and no host round trip
+inside the loop (`ShardedGriffinLim`); `griffinlim_fragments_emulated` runs the same protocol with all fragments in
+one launch on one GPU (links point into the same workspace), which is how the single-GPU tests cover it.
+Reference semantics: src/utils.py:245-276 (`get_spectrograms`), :281-328 (`spectrogram2wav`) on a long file.
 """
 from __future__ import annotations
 
@@ -79,4 +85,127 @@ def spectrograms_long(wave, rank=0, world=1, precision=None, do_trim=True):
     return mel, mag, (a, b), T
 
 
-__all__ = ["frame_ranges", "chunk_for_range", "spectrograms_long", "HALO"]
+SEAM0 = (ap.n_fft - ap.win_length) // 2           # 473: padded position of a frame's first tap relative to 275 t
+GL_MIN_FRAGMENT = 9
+
+
+def _links_for(eng, my_frames, my_base, left=None, right=None, momentum=0.0):
+    """Link descriptors of ONE fragment (index 0 of this rank's call).  left / right = (partner workspace base address as
+    mapped here, partner's fragment size) or None.  Mailbox slots: 0 = my left seam, 1 = my right seam."""
+    links = []
+    if left is not None:
+        base, n_l = left
+        lay = eng.gl_layout([n_l], momentum)
+        links.append({"fragment": 0, "side": 0, "my_mail": 0, "peer_mail": base + lay[3] + 4 * 1,
+                      "peer_ola": [base + lay[k] + 4 * (HOP * n_l + SEAM0) for k in range(3)]})
+    if right is not None:
+        base, n_r = right
+        lay = eng.gl_layout([n_r], momentum)
+        links.append({"fragment": 0, "side": 1, "my_mail": 1, "peer_mail": base + lay[3] + 4 * 0,
+                      "peer_ola": [base + lay[k] + 4 * SEAM0 for k in range(3)]})
+    return links
+
+
+class ShardedGriffinLim:
+    """Griffin-Lim on ONE long spectrogram of T frames, frames sharded by contiguous ranges over the ranks of the default
+    process group (one process per GPU).  Construct once per (T, momentum) on every rank (collective: exchanges the CUDA
+    IPC handles of the workspaces), then `run()` any number of times."""
+
+    def __init__(self, T, rank, world, momentum=0.0):
+        import torch.distributed as dist
+        self.eng = get_engine()
+        self.T, self.rank, self.world, self.momentum = int(T), int(rank), int(world), float(momentum)
+        self.ranges = frame_ranges(self.T, self.world)
+        self.a, self.b = self.ranges[self.rank]
+        sizes = [e - s for s, e in self.ranges]
+        if self.world > 1 and min(sizes) < GL_MIN_FRAGMENT:
+            raise ValueError("every rank needs at least %d frames" % GL_MIN_FRAGMENT)
+        lay = self.eng.gl_layout([self.b - self.a], self.momentum)
+        self.ws, handle = self.eng.peer_alloc(lay[4])
+        self._opened = []
+        self.links = []
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, handle)
+            left = right = None
+            if self.rank > 0:
+                base = self.eng.peer_open(handles[self.rank - 1]); self._opened.append(base)
+                left = (base, sizes[self.rank - 1])
+            if self.rank + 1 < self.world:
+                base = self.eng.peer_open(handles[self.rank + 1]); self._opened.append(base)
+                right = (base, sizes[self.rank + 1])
+            self.links = _links_for(self.eng, self.b - self.a, self.ws, left, right, self.momentum)
+            dist.barrier()
+        self.epoch = 1
+
+    def run(self, mag_rows, n_iter, angles0_rows=None, power=ap.power, raw_out=None):
+        """mag_rows: this rank's rows [a, b) of the normalised magnitude spectrogram (device float32 [b - a, 1025]).
+        Returns this rank's owned samples of istft(S * angles) after n_iter iterations (device float32), asynchronous."""
+        raw, _ = self.eng.griffinlim_fragments(mag_rows, [self.b - self.a], [self.a], [self.T], self.links, epoch=self.epoch,
+                                               n_iter=n_iter, momentum=self.momentum, angles0=angles0_rows, power=power,
+                                               workspace=self.ws, raw_out=raw_out)
+        self.epoch += int(n_iter) + 2
+        return raw
+
+    def sample_range(self):
+        return self.eng.fragment_samples(self.a, self.b - self.a, self.T)
+
+    def gather_deemph_trim(self, raw, deemphasis=True, want_trim=True):
+        """Epilogue (utils.py:301-306): the ranks' samples are gathered on rank 0 (off the iteration path), de-emphasised in
+        float64 and trimmed there.  Returns (wav float32 device tensor, (start, end)) on rank 0, (None, None) elsewhere."""
+        import torch.distributed as dist
+        L = HOP * (self.T - 1)
+        if self.world > 1:
+            counts = [self.eng.fragment_samples(s, e - s, self.T) for s, e in self.ranges]
+            parts = [torch.empty(e - s, dtype=torch.float32, device=raw.device) for s, e in counts] if self.rank == 0 else None
+            dist.gather(raw, parts, dst=0)
+            if self.rank != 0:
+                return None, None
+            raw = torch.cat(parts)
+        off = torch.tensor([0, L], dtype=torch.int64, device=raw.device)
+        wav, bounds = self.eng.deemph_trim(raw, off, L, deemphasis=deemphasis, want_trim=want_trim)
+        if not want_trim:
+            return wav, (0, L)
+        s, e = (int(v) for v in bounds.cpu().numpy()[0])
+        return wav, (s, e)
+
+    def close(self):
+        for base in self._opened:
+            self.eng.peer_close(base)
+        self._opened = []
+        if self.ws:
+            self.eng.peer_free(self.ws)
+            self.ws = 0
+
+
+_EMU_EPOCH = [1]
+
+
+def griffinlim_fragments_emulated(mag, world, n_iter, momentum=0.0, angles0=None, power=ap.power):
+    """The sharded run's protocol on ONE GPU: the T frames of `mag` (device float32 [T, 1025]) cut into `world` fragments
+    that are processed by one launch, every cut a linked seam whose two copies live in the same workspace.  Returns the
+    raw (normalised, not de-emphasised) waveform [275 (T - 1)] as a device tensor."""
+    eng = get_engine()
+    T = int(mag.shape[0])
+    ranges = frame_ranges(T, world)
+    frames = [e - s for s, e in ranges]
+    t0 = [s for s, _ in ranges]
+    if world > 8 or (world > 1 and min(frames) < GL_MIN_FRAGMENT):
+        raise ValueError("at most 8 fragments of at least %d frames" % GL_MIN_FRAGMENT)
+    lay = eng.gl_layout(frames, momentum)
+    base = eng._workspace("glf", lay[4], zero=True).data_ptr()
+    pad = eng.gl_pad_offsets(frames)
+    links = []
+    for i in range(world - 1):
+        slot_l, slot_r = 2 * i, 2 * i + 1                                  # mailboxes of the left / right side of cut i
+        links.append({"fragment": i, "side": 1, "my_mail": slot_l, "peer_mail": base + lay[3] + 4 * slot_r,
+                      "peer_ola": [base + lay[k] + 4 * (int(pad[i + 1]) + SEAM0) for k in range(3)]})
+        links.append({"fragment": i + 1, "side": 0, "my_mail": slot_r, "peer_mail": base + lay[3] + 4 * slot_l,
+                      "peer_ola": [base + lay[k] + 4 * (int(pad[i]) + HOP * frames[i] + SEAM0) for k in range(3)]})
+    raw, _ = eng.griffinlim_fragments(mag, frames, t0, [T] * world, links, epoch=_EMU_EPOCH[0], n_iter=n_iter, momentum=momentum,
+                                      angles0=angles0, power=power, workspace=base)
+    _EMU_EPOCH[0] += int(n_iter) + 2
+    return raw
+
+
+__all__ = ["frame_ranges", "chunk_for_range", "spectrograms_long", "HALO", "ShardedGriffinLim", "griffinlim_fragments_emulated"]

@@ -143,7 +143,9 @@ def stft(y, nfft=n_fft, hop=hop_length, win=win_length):
     ypad = np.pad(np.asarray(y), nfft // 2, mode="reflect")
     frames = _frame(ypad, nfft, hop)                               # (nfft, T), dtype of y
     out = np.empty((1 + nfft // 2, frames.shape[1]), dtype=np.complex64, order="F")
-    out[:] = np.fft.rfft(w * frames, axis=0)                       # float64 -> complex64
+    # numpy >= 2.0 transforms float32 / complex64 input in single precision; the reference's numpy 1.19 (requirements.txt:2)
+    # always transforms in float64 -- force it (w is float64, so the product already is)
+    out[:] = np.fft.rfft((w * frames).astype(np.float64, copy=False), axis=0)   # float64 -> complex64
     return out
 
 
@@ -162,7 +164,8 @@ def istft(X, hop=hop_length, win=win_length, dtype=np.float32):
     T = X.shape[1]
     w = pad_center(hann_periodic(win), nfft)[:, None]
     y = np.zeros(nfft + hop * (T - 1), dtype=dtype)
-    ytmp = w * np.fft.irfft(X, axis=0)                             # float64
+    # float64 irfft as under the reference's numpy 1.19 (numpy >= 2.0 would run a complex64 input in single precision)
+    ytmp = w * np.fft.irfft(np.asarray(X).astype(np.complex128), axis=0)
     for t in range(T):
         s = t * hop
         y[s:s + nfft] += ytmp[:, t]
@@ -259,6 +262,10 @@ def get_spectrograms(fpath):
 def denormalise(mag):
     """utils.py:289-298: [T,1025] normalised -> S[1025,T] = (10^((clip*100-100+20)*0.05))^1.2."""
     mag = np.asarray(mag, dtype=np.float32).T
+    # float32 throughout, exactly the reference's statements (utils.py:292-298).  NOTE: the zero-phase start of
+    # utils.griffin_lim is ill-conditioned -- one ulp of S moves the 60-iteration waveform by about -72 dB (measured by
+    # swapping numpy's powf for a correctly rounded one; DESIGN.md section 3) -- so the last bit of these powf calls, which
+    # differs between numpy versions / libms, is visible in Griffin-Lim's output at that level.
     mag = (np.clip(mag, 0, 1) * max_db) - max_db + ref_db
     mag = np.power(10.0, mag * 0.05)
     return (mag ** power).astype(np.float32)

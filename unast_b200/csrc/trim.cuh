@@ -155,10 +155,13 @@ __global__ void gl_prepare_kernel(const float* __restrict__ mag, long long total
         const long long r = i / NBINS;
         const int k = (int)(i - r * NBINS);
         if (power == 0.0f) { S[r * S_STRIDE + k] = mag[i]; continue; }   // input already is the linear target magnitude
-        float m = fminf(fmaxf(mag[i], 0.0f), 1.0f);
-        m = m * 100.0f - 100.0f + 20.0f;
-        const float a = powf(10.0f, m * 0.05f);
-        S[r * S_STRIDE + k] = powf(a, power);
+        // numpy's float32 sequence, one rounding per operation (no FMA contraction); the two powf of the reference
+        // (glibc: correctly rounded) as float64 pow rounded once -- the zero-phase start of utils.griffin_lim amplifies an
+        // ulp of S to ~ -90 dB of the first estimate, so S has to match to the last bit, not to a few ulp
+        const float c = fminf(fmaxf(mag[i], 0.0f), 1.0f);
+        const float m = __fadd_rn(__fsub_rn(__fmul_rn(c, 100.0f), 100.0f), 20.0f);
+        const float a = (float)pow(10.0, (double)__fmul_rn(m, 0.05f));
+        S[r * S_STRIDE + k] = (float)pow((double)a, (double)power);
     }
 }
 

@@ -88,15 +88,17 @@ __device__ __forceinline__ bool gl_wait(const int* p, int target, int* abort_fla
     if (lane == 0) {
         unsigned long long t0 = 0;
         int spins = 0;
-        while ((SYS ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - target < 0) {
+        // relaxed polls (an acquire load invalidates the L1 on every poll), one acquire fence once the value is there
+        while ((SYS ? ld_relaxed_sys(p) : ld_relaxed_gpu(p)) - target < 0) {
             if ((++spins & 63) == 0) {
                 if (*reinterpret_cast<volatile int*>(abort_flag)) { ok = 0; break; }
                 const unsigned long long now = global_timer_ns();
                 if (t0 == 0) t0 = now;
                 else if (now - t0 > GL_WAIT_NS) { atomicCAS(err, ERR_NONE, ERR_SYNC); atomicExch(abort_flag, 1); ok = 0; break; }
             }
-            __nanosleep(32);
+            __nanosleep(20);
         }
+        if (SYS) __threadfence_system(); else __threadfence();
     }
     ok = __shfl_sync(0xffffffffu, ok, 0);
     return ok != 0;
@@ -130,6 +132,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
     // this warp's run of frames (equal shares of a cost that weights edge frames; resolved once on the host)
     const int gw = blockIdx.x * GL_WARPS + warp;
     if (gw >= P.n_runs) return;
+    const int cta_threads = 32 * min(GL_WARPS, P.n_runs - blockIdx.x * GL_WARPS);   // warps of this CTA that own a run
+    bool dead = false;                                                   // a wait timed out: keep the barriers company, do nothing
     const int4 run = P.runs[gw];
     const int f0 = run.x, f1 = run.y;
     const int link_l = (run.w & 0xffff) - 1, link_r = (run.w >> 16) - 1;
@@ -151,7 +155,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
         bool ok = true;
         if (link_l >= 0) ok = gl_wait<true>(poll_l, P.epoch, P.abort, P.err, lane);
         if (ok && link_r >= 0) ok = gl_wait<true>(poll_r, P.epoch, P.abort, P.err, lane);
-        if (!ok) return;
+        dead = !ok;
     }
 
 #pragma unroll 1
@@ -166,8 +170,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
 
         // target-magnitude row of the first frame (every later row is fetched one frame ahead)
         __syncwarp();
-        if (lane == 0) tma_load_1d(srow, P.S + (size_t)f0 * S_STRIDE, GLP_SROW_BYTES, bar_s);
-        if (iter_mode) {
+        if (!dead && lane == 0) tma_load_1d(srow, P.S + (size_t)f0 * S_STRIDE, GLP_SROW_BYTES, bar_s);
+        if (iter_mode && !dead) {
             // both neighbours have finished iteration it - 1: everything this iteration reads is complete, and
             // nobody still reads what it overwrites or re-zeroes
             bool ok = true;
@@ -175,8 +179,13 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                                          : gl_wait<false>(poll_l, P.epoch + it, P.abort, P.err, lane);
             if (ok && poll_r) ok = link_r >= 0 ? gl_wait<true>(poll_r, P.epoch + it, P.abort, P.err, lane)
                                                : gl_wait<false>(poll_r, P.epoch + it, P.abort, P.err, lane);
-            if (!ok) return;
+            dead = !ok;
         }
+        // The CTA's warps (16 adjacent runs) start every iteration together: left alone they drift through the 98 KB loop
+        // body and thrash the instruction cache (r3f capture: 1.5 warps per issue cycle stalled on instruction fetch against
+        // 0.37 when a launch boundary realigned them every iteration).
+        asm volatile("bar.sync 1, %0;" ::"r"(cta_threads) : "memory");
+        if (dead) continue;
         // momentum: pull a frame's previous estimate (8,200 bytes) into L2 one frame before its bins are read
         auto prefetch_prev = [&](int f) {
             if (MOMENTUM && iter_mode && !first_iter) {

@@ -160,8 +160,8 @@ __global__ void gl_prepare_kernel(const float* __restrict__ mag, long long total
         // ulp of S to ~ -90 dB of the first estimate, so S has to match to the last bit, not to a few ulp
         const float c = fminf(fmaxf(mag[i], 0.0f), 1.0f);
         const float m = __fadd_rn(__fsub_rn(__fmul_rn(c, 100.0f), 100.0f), 20.0f);
-        const float a = (float)pow(10.0, (double)__fmul_rn(m, 0.05f));
-        S[r * S_STRIDE + k] = (float)pow((double)a, (double)power);
+        const float a = (float)exp10((double)__fmul_rn(m, 0.05f));
+        S[r * S_STRIDE + k] = (float)exp2((double)power * log2((double)a));      // a^power; ~1e-15 before the rounding to float
     }
 }
 

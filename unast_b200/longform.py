@@ -156,18 +156,32 @@ class ShardedGriffinLim:
         import torch.distributed as dist
         L = HOP * (self.T - 1)
         if self.world > 1:
-            counts = [self.eng.fragment_samples(s, e - s, self.T) for s, e in self.ranges]
-            parts = [torch.empty(e - s, dtype=torch.float32, device=raw.device) for s, e in counts] if self.rank == 0 else None
-            dist.gather(raw, parts, dst=0)
+            raw = self.gather_rows(raw)
             if self.rank != 0:
                 return None, None
-            raw = torch.cat(parts)
         off = torch.tensor([0, L], dtype=torch.int64, device=raw.device)
         wav, bounds = self.eng.deemph_trim(raw, off, L, deemphasis=deemphasis, want_trim=want_trim)
         if not want_trim:
             return wav, (0, L)
         s, e = (int(v) for v in bounds.cpu().numpy()[0])
         return wav, (s, e)
+
+    def gather_rows(self, x):
+        """Concatenation over the ranks (in rank order) of per-rank tensors whose first dimensions differ, on rank 0 (None
+        elsewhere).  torch.distributed.gather wants equal shapes: pad to the longest, gather, cut."""
+        import torch.distributed as dist
+        n = torch.tensor([x.shape[0]], dtype=torch.int64, device=x.device)
+        ns = [torch.zeros_like(n) for _ in range(self.world)]
+        dist.all_gather(ns, n)
+        ns = [int(v.item()) for v in ns]
+        m = max(ns)
+        pad = torch.zeros((m,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+        pad[:x.shape[0]] = x
+        parts = [torch.empty_like(pad) for _ in range(self.world)] if self.rank == 0 else None
+        dist.gather(pad, parts, dst=0)
+        if self.rank != 0:
+            return None
+        return torch.cat([p[:k] for p, k in zip(parts, ns)])
 
     def close(self):
         for base in self._opened:

@@ -631,3 +631,42 @@ def test_sharded_griffin_lim_protocol_emulated_on_one_gpu():
     wav, bounds = eng.deemph_trim(torch.from_numpy(base).cuda(), torch.tensor([0, L], dtype=torch.int64, device="cuda"), L)
     s, e = (int(v) for v in bounds.cpu().numpy()[0])
     assert np.array_equal(wav.cpu().numpy()[s:e], full)
+
+
+def test_prepare_streams_files_like_np_save(tmp_path):
+    """prepare_data.prepare(): reader thread -> pinned staging -> GPU -> writer threads; the .npy files must be byte-identical
+    to what np.save writes for the arrays get_spectrograms returns (prepare_data.py:33-34), over several chunks."""
+    from unast_b200 import prepare_data, synth, utils as U
+    ids = ["LJ%03d" % i for i in range(11)]
+    waves = _clips([(1.1 + 0.13 * i, 200 + i) for i in range(11)])
+    for i, w in zip(ids, waves):
+        synth.write_wav_pcm16(str(tmp_path / (i + ".wav")), w)
+    (tmp_path / "metadata.csv").write_text("".join("%s|x|x\n" % i for i in ids))
+    n = prepare_data.prepare(str(tmp_path / "metadata.csv"), str(tmp_path), batch_size=3, writers=2)   # 4 chunks in flight
+    assert n == 11
+    for i in ids:
+        mel, mag = U.get_spectrograms(str(tmp_path / (i + ".wav")))
+        np.save(str(tmp_path / "ref.pt"), mel)
+        np.save(str(tmp_path / "ref.mag"), mag)
+        assert open(str(tmp_path / (i + ".pt.npy")), "rb").read() == open(str(tmp_path / "ref.pt.npy"), "rb").read()
+        assert open(str(tmp_path / (i + ".mag.npy")), "rb").read() == open(str(tmp_path / "ref.mag.npy"), "rb").read()
+
+
+def test_vocode_tensors_device_entry_matches_file_path():
+    """Device-tensor hand-off (inf_vocoder.py:48-64 -> gl_vocoder.py:15-32 without the .npy round trip): a padded
+    [B, T_max, 1025] device batch gives the waveforms vocode_arrays gives for the same magnitudes and seed."""
+    torch = _torch()
+    from unast_b200 import gl_vocoder as GV
+    mags = _mags([(1.3, 31), (1.9, 32), (1.1, 33)])
+    frames = [m.shape[0] for m in mags]
+    pad = np.zeros((3, max(frames), 1025), np.float32)
+    for b, m in enumerate(mags):
+        pad[b, :frames[b]] = m
+    np.random.seed(5)
+    ref = GV.vocode_arrays(mags)
+    np.random.seed(5)
+    wav, off, bounds = GV.vocode_tensors(torch.from_numpy(pad).cuda(), frames)
+    wav, bounds = wav.cpu().numpy(), bounds.cpu().numpy()
+    for b in range(3):
+        y = wav[off[b]:off[b + 1]][bounds[b, 0]:bounds[b, 1]]
+        assert np.array_equal(y, ref[b])

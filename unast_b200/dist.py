@@ -41,6 +41,47 @@ def init_from_env(backend=None):
     return rank, local_rank, world
 
 
+def pin_to_local_cores(local_rank, local_world):
+    """Give this rank a disjoint set of host cores on its GPU's NUMA node before it allocates pinned buffers or starts its
+    reader / writer threads: ranks that share one affinity mask (every GPU of the round-1 box reported CPU affinity 0-31,
+    NUMA 0) otherwise migrate across each other's cores and stage through each other's memory.  Best effort; returns what
+    was done for the bench record."""
+    info = {"cores_before": len(os.sched_getaffinity(0))}
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        node_cores = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+            bus = bus.decode() if isinstance(bus, bytes) else bus
+            bus = bus.lower()
+            if len(bus.split(":")[0]) == 8:                            # nvml prints a 32-bit domain, sysfs a 16-bit one
+                bus = bus[4:]
+            with open("/sys/bus/pci/devices/%s/numa_node" % bus) as fh:
+                node = int(fh.read().strip())
+            info["numa_node"] = node
+            if node >= 0:
+                with open("/sys/devices/system/node/node%d/cpulist" % node) as fh:
+                    lst = set()
+                    for part in fh.read().strip().split(","):
+                        a, _, b = part.partition("-")
+                        lst.update(range(int(a), int(b or a) + 1))
+                node_cores = [c for c in cores if c in lst]
+        except Exception as e:                                          # no nvml / sysfs: fall back to the affinity mask
+            info["numa_lookup"] = repr(e)[:80]
+        use = node_cores if node_cores else cores
+        per = len(use) // max(1, local_world)
+        if per >= 1 and local_world > 1:
+            mine = use[local_rank * per:(local_rank + 1) * per]
+            os.sched_setaffinity(0, mine)
+            info["cores"] = [mine[0], mine[-1]]
+        info["cores_after"] = len(os.sched_getaffinity(0))
+    except Exception as e:
+        info["error"] = repr(e)[:80]
+    return info
+
+
 def _device_for_collectives():
     if dist.is_initialized() and dist.get_backend() == "nccl":
         return torch.device("cuda", torch.cuda.current_device())

@@ -50,6 +50,41 @@ def read_wav(path, expect_sr=ap.sr):
     return np.ascontiguousarray(y), rate
 
 
+def wav_info(path, expect_sr=ap.sr):
+    """(samples per channel, numpy dtype of read_wav's result, channels) from the header alone (no payload read)."""
+    with open(path, "rb") as fh:
+        head = fh.read(12)
+        if len(head) < 12 or head[:4] != b"RIFF" or head[8:12] != b"WAVE":
+            raise ValueError("%s: not a RIFF/WAVE file" % path)
+        fmt = None
+        while True:
+            ch = fh.read(8)
+            if len(ch) < 8:
+                raise ValueError("%s: missing fmt or data chunk" % path)
+            cid, sz = ch[:4], struct.unpack("<I", ch[4:])[0]
+            if cid == b"fmt ":
+                body = fh.read(sz + (sz & 1))
+                fmt = struct.unpack("<HHIIHH", body[:16])
+            elif cid == b"data":
+                if fmt is None:
+                    raise ValueError("%s: data chunk before fmt" % path)
+                tag, nch, rate, _, align, bits = fmt
+                if expect_sr is not None and rate != expect_sr:
+                    raise ValueError("%s: sample rate %d != %d; resampling (librosa kaiser_best) is out of scope" % (path, rate, expect_sr))
+                dt = np.int16 if (tag == 1 and bits == 16 and nch == 1) else np.float32
+                return sz // max(1, align), dt, nch
+            else:
+                fh.seek(sz + (sz & 1), 1)
+
+
+def npy_header(shape, fortran_order):
+    """The bytes np.save writes before a float32 payload of this shape / order (format 1.0, numpy's own writer)."""
+    import io
+    buf = io.BytesIO()
+    np.lib.format.write_array_header_1_0(buf, {"descr": "<f4", "fortran_order": bool(fortran_order), "shape": tuple(int(v) for v in shape)})
+    return buf.getvalue()
+
+
 def write_wav_pcm16(path, y, rate=ap.sr):
     """16-bit PCM WAV, what ``sf.write(path, wav, sr)`` (gl_vocoder.py:34) produces: python-soundfile's default subtype
     for ``.wav`` is PCM_16 whatever the array dtype, and libsndfile converts floats (normalised, clipping off -- the

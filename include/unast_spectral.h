@@ -169,6 +169,19 @@ size_t unast_mel_augment_workspace_bytes(int B);
 int unast_mel_augment(unast_ctx* ctx, const float* x, int B, int T, int D, const int32_t* spans, const float* keep,
                       int replace_with_zero, float* out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* The masking ops above fused with the first layer of SpeechPrenet (module.py:93-95: fc1 = Linear(num_mels -> s_pre_hid),
+ * ReLU), on the tensor cores (tcgen05.mma, A operand in tensor memory, float32 fidelity by operand splitting):
+ *     y[b][t][:] = relu(W ((t in a span ? fill_b : x[b][t][:]) * keep[b][t]) + bias)          x: [B][T][80], y: [B][T][n_out]
+ * unast_prenet_pack turns nn.Linear's weight [n_out][80] (+ bias [n_out] or NULL) into the image the kernel keeps in shared
+ * memory (unast_prenet_packed_bytes(n_out) bytes, device, 16-byte aligned; n_out a multiple of 16, <= 256); repack after
+ * every weight update.  spans / keep / replace_with_zero as in unast_mel_augment; relu = 0 returns the pre-activation.
+ * Dropout (module.py:96) is left to the caller.  workspace >= unast_mel_augment_workspace_bytes(B). */
+size_t unast_prenet_packed_bytes(int n_out);
+int unast_prenet_pack(unast_ctx* ctx, const float* weight, const float* bias, int n_out, void* packed_out, void* stream);
+int unast_mel_prenet_fc1(unast_ctx* ctx, const float* x, int B, int T, const int32_t* spans, const float* keep,
+                         int replace_with_zero, const void* packed, int n_out, int relu, float* y, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
 /* ---- diagnostics (used by the test-suite to pin the FFT core on its own) --------------------- */
 
 /* frames: float[F][2048] whose samples [1102, 2048) are zero; out: complex64[F][1025] = rfft(frame). */

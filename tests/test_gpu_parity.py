@@ -670,3 +670,33 @@ def test_vocode_tensors_device_entry_matches_file_path():
     for b in range(3):
         y = wav[off[b]:off[b + 1]][bounds[b, 0]:bounds[b, 1]]
         assert np.array_equal(y, ref[b])
+
+
+def test_prenet_fc1_on_tensor_cores_matches_float32_torch(engine):
+    """masking -> Linear(80 -> 256 / 128) + bias -> ReLU (module.py:93-95) in one tcgen05 kernel against plain float32 torch:
+    operand splitting keeps float32 fidelity (2e-6 of the row's |x| . |w| scale; torch's own float32 GEMM is within 4x)."""
+    torch = _torch()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    rng = np.random.RandomState(12)
+    for (B, T, N) in ((5, 333, 256), (3, 129, 128), (1, 7, 256)):
+        x = torch.from_numpy(rng.uniform(0, 1, size=(B, T, 80)).astype(np.float32)).cuda()
+        W = torch.from_numpy((rng.randn(N, 80) / 9).astype(np.float32)).cuda()
+        bias = torch.from_numpy(rng.randn(N).astype(np.float32)).cuda()
+        lens = np.full(B, T)
+        _seed_all(21)
+        spans = torch.from_numpy(so.specaugment_spans(lens) if T > 120 else np.zeros((B, 4), np.int32)).cuda()
+        keep = (torch.rand((B, T), device="cuda") > 0.3).float()
+        packed, n_out = engine.prenet_pack(W, bias)
+        y = engine.mel_prenet_fc1(x, packed, n_out, spans=spans, keep=keep)
+        xm = engine.mel_augment(x, spans=spans, keep=keep)                          # the masking kernel, already pinned
+        ref = torch.relu(torch.nn.functional.linear(xm.double(), W.double(), bias.double())).float()
+        scale = (xm.abs() @ W.abs().T + bias.abs()).clamp_min(1e-6)
+        assert y.shape == ref.shape
+        assert ((y - ref).abs() / scale).max().item() <= 2e-6
+        pre = engine.mel_prenet_fc1(x, packed, n_out, relu=False)                    # no masks, pre-activation
+        ref2 = torch.nn.functional.linear(x.double(), W.double(), bias.double()).float()
+        assert ((pre - ref2).abs() / (x.abs() @ W.abs().T + bias.abs())).max().item() <= 2e-6
+        ref32 = torch.nn.functional.linear(x, W, bias)                               # torch's own float32 GEMM is no closer
+        # float32-class, not TF32-class (a single TF32 pass is ~1e-3): what remains is the tensor cores' truncating float32
+        # accumulation over 30 instructions (~20 ulp of the sum), within 10x of cuBLAS's float32 GEMM
+        assert (pre - ref2).abs().max().item() <= 10 * (ref32 - ref2).abs().max().item() + 1e-6

@@ -44,6 +44,9 @@ SYMBOLS = [
     ("unast_peer_free", _i, [_vp, _vp]),
     ("unast_mel_augment_workspace_bytes", _sz, [_i]),
     ("unast_mel_augment", _i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
+    ("unast_prenet_packed_bytes", _sz, [_i]),
+    ("unast_prenet_pack", _i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    ("unast_mel_prenet_fc1", _i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp, _i, _i, _vp, _vp, _sz, _vp]),
     ("unast_debug_rfft", _i, [_vp, _vp, _i, _i, _vp, _vp]),
     ("unast_debug_irfft", _i, [_vp, _vp, _i, _vp, _vp]),
     ("unast_debug_pipe_peak", _i, [_vp, _i, _i, _vp, C.POINTER(C.c_double), _vp]),

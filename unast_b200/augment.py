@@ -98,4 +98,30 @@ def specaugment_noise(mel, mel_len, freq_mask=20, time_mask=100, replace_with_ze
                            replace_with_zero=replace_with_zero)
 
 
-__all__ = ["specaugment", "noise_fn", "specaugment_noise", "draw_specaugment_spans"]
+class PrenetFC1:
+    """specaugment -> noise_fn -> SpeechPrenet.fc1 -> ReLU (src/train.py:236, src/network.py:205, src/module.py:93-95) as ONE
+    pass over the padded mel batch, the Linear on the tensor cores (csrc/prenet.cuh).  Inference / frozen-prenet use: the
+    kernel has no backward; Dropout (module.py:96) is applied by the caller.  Draw order: specaugment's, then noise_fn's."""
+
+    def __init__(self, weight, bias=None):
+        self.eng = get_engine()
+        self.packed, self.n_out = self.eng.prenet_pack(weight, bias)
+
+    def repack(self, weight, bias=None):
+        self.packed, self.n_out = self.eng.prenet_pack(weight, bias)
+
+    def __call__(self, mel, mel_len=None, augment=True, noise=True, freq_mask=20, time_mask=100, replace_with_zero=False, mask_p=.3,
+                 relu=True):
+        eng = self.eng
+        spans = keep = None
+        if augment:
+            spans = torch.from_numpy(draw_specaugment_spans(mel_len, freq_mask, time_mask)).to(eng.device)
+        if noise:
+            gen = torch.zeros((mel.shape[0], mel.shape[1]), device=mel.device)
+            gen.fill_(1 - mask_p)
+            keep = torch.bernoulli(gen).to(eng.device).contiguous()
+        x = mel.detach().to(eng.device).contiguous()
+        return eng.mel_prenet_fc1(x, self.packed, self.n_out, spans=spans, keep=keep, replace_with_zero=replace_with_zero, relu=relu)
+
+
+__all__ = ["specaugment", "noise_fn", "specaugment_noise", "draw_specaugment_spans", "PrenetFC1"]

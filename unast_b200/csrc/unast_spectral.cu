@@ -13,6 +13,7 @@
 #include "griffinlim_pk.cuh"
 #include "trim.cuh"
 #include "augment.cuh"
+#include "prenet.cuh"
 
 using namespace unast;
 
@@ -388,6 +389,7 @@ int unast_create(int device, unast_ctx** out) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<float, FE32_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<float, FE32_WARPS>::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, FE64_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, FE64_WARPS>::bytes);
     c->items.w = c->it_w; c->items.k0 = c->it_k0; c->items.mel = c->it_mel;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(prenet_fc1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pre_packed_bytes(PRE_MAXN) + 64);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
@@ -885,6 +887,47 @@ int unast_mel_augment(unast_ctx* c, const float* x, int B, int T, int D, const i
     if (per < 1) per = 1;
     aug_apply_kernel<<<dim3((unsigned)per, B), AUG_THREADS, 0, st>>>(x, out, T, D, spans, keep, need_mean ? parts : nullptr,
                                                                      replace_with_zero);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+// ---- masking ops + first prenet layer on the tensor cores (8(f) rank 2) ----
+size_t unast_prenet_packed_bytes(int n_out) {
+    if (n_out < 16 || n_out > PRE_MAXN || (n_out & 15)) return 0;
+    return (size_t)pre_packed_bytes(n_out);
+}
+
+int unast_prenet_pack(unast_ctx* c, const float* weight, const float* bias, int n_out, void* packed_out, void* stream) {
+    if (!c || !weight || !packed_out || unast_prenet_packed_bytes(n_out) == 0) return fail(UNAST_E_ARG, "unast_prenet_pack: bad argument (n_out must be a multiple of 16, 16..256)");
+    if ((uintptr_t)packed_out & 15) return fail(UNAST_E_ARG, "unast_prenet_pack: packed_out must be 16-byte aligned");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
+    const int n = n_out * PRE_K;
+    prenet_pack_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(weight, bias, n_out, (unsigned char*)packed_out);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+int unast_mel_prenet_fc1(unast_ctx* c, const float* x, int B, int T, const int32_t* spans, const float* keep, int replace_with_zero,
+                         const void* packed, int n_out, int relu, float* y, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!c || !x || !y || !packed || B <= 0 || T <= 0 || unast_prenet_packed_bytes(n_out) == 0) return fail(UNAST_E_ARG, "unast_mel_prenet_fc1: bad argument");
+    if (B > 65535) return fail(UNAST_E_ARG, "unast_mel_prenet_fc1: B must be <= 65535");
+    if (((uintptr_t)x | (uintptr_t)y | (uintptr_t)packed) & 15) return fail(UNAST_E_ARG, "unast_mel_prenet_fc1: x, y and packed must be 16-byte aligned");
+    if (spans && ((uintptr_t)spans & 15)) return fail(UNAST_E_ARG, "unast_mel_prenet_fc1: spans must be 16-byte aligned");
+    const bool need_mean = spans && !replace_with_zero;
+    if (need_mean && (!workspace || workspace_bytes < unast_mel_augment_workspace_bytes(B))) return fail(UNAST_E_WORKSPACE, "unast_mel_prenet_fc1: workspace too small");
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
+    cudaStream_t st = (cudaStream_t)stream;
+    double* parts = (double*)workspace;
+    if (need_mean) aug_sum_kernel<<<dim3(AUG_PARTS, B), AUG_THREADS, 0, st>>>(x, (long long)T * PRE_K, parts);
+    PrenetParams P;
+    P.x = x; P.y = y; P.B = B; P.T = T; P.N = n_out; P.spans = spans; P.keep = keep; P.parts = need_mean ? parts : nullptr;
+    P.replace_with_zero = replace_with_zero; P.relu = relu; P.packed = (const unsigned char*)packed;
+    const long long tiles = ((long long)B * T + PRE_TILE_M - 1) / PRE_TILE_M;
+    const int grid = (int)std::min<long long>(tiles, c->num_sms);
+    const size_t smem = ((size_t)pre_packed_bytes(n_out) + 15) / 16 * 16 + 32;
+    prenet_fc1_kernel<<<grid, PRE_THREADS, smem, st>>>(P);
     CU(cudaGetLastError());
     return UNAST_OK;
 }

@@ -264,6 +264,39 @@ class SpectralEngine:
         self.launches += 2 if (spans is not None and not replace_with_zero) else 1
         return out
 
+    def prenet_pack(self, weight, bias=None):
+        """nn.Linear(80 -> n_out) parameters -> the shared-memory image unast_mel_prenet_fc1 uses (repack after an update)."""
+        if weight.dtype != torch.float32 or weight.dim() != 2 or weight.shape[1] != NMELS:
+            raise TypeError("weight must be a float32 [n_out, 80] tensor")
+        n_out = int(weight.shape[0])
+        nbytes = self.lib.unast_prenet_packed_bytes(n_out)
+        if nbytes == 0:
+            raise ValueError("n_out must be a multiple of 16 in 16..256")
+        w = weight.detach().to(self.device).contiguous()
+        b = bias.detach().to(self.device, torch.float32).contiguous() if bias is not None else None
+        packed = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        L.check(self.lib.unast_prenet_pack(self.h, _ptr(w), _ptr(b), n_out, _ptr(packed), self._stream()))
+        self.launches += 1
+        return packed, n_out
+
+    def mel_prenet_fc1(self, x, packed, n_out, spans=None, keep=None, replace_with_zero=False, relu=True, out=None):
+        """relu(fc1((row in a span ? fill : x) * keep)) for a float32 [B, T, 80] device batch -> [B, T, n_out] (csrc/prenet.cuh)."""
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.dim() != 3 or x.shape[2] != NMELS:
+            raise TypeError("x must be a contiguous float32 [B, T, 80] tensor")
+        B, T = int(x.shape[0]), int(x.shape[1])
+        if spans is not None and (spans.dtype != torch.int32 or tuple(spans.shape) != (B, 4) or not spans.is_contiguous()):
+            raise TypeError("spans must be a contiguous int32 [B, 4] tensor")
+        if keep is not None and (keep.dtype != torch.float32 or tuple(keep.shape) != (B, T) or not keep.is_contiguous()):
+            raise TypeError("keep must be a contiguous float32 [B, T] tensor")
+        if out is None:
+            out = torch.empty((B, T, n_out), dtype=torch.float32, device=self.device)
+        nbytes = self.lib.unast_mel_augment_workspace_bytes(B)
+        ws = self._workspace("aug", nbytes)
+        L.check(self.lib.unast_mel_prenet_fc1(self.h, _ptr(x), B, T, _ptr(spans), _ptr(keep), 1 if replace_with_zero else 0, _ptr(packed),
+                                              int(n_out), 1 if relu else 0, _ptr(out), _ptr(ws), nbytes, self._stream()))
+        self.launches += 2 if (spans is not None and not replace_with_zero) else 1
+        return out
+
     # -- diagnostics -------------------------------------------------------------------------------
     def debug_rfft(self, frames, precision="f32"):
         F = frames.shape[0]

@@ -29,6 +29,49 @@ template <int J> __device__ __forceinline__ float& imB(Pk& p) { if constexpr (J 
 __device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
 __device__ __forceinline__ float2 dup2(float c) { return make_float2(c, c); }
 
+// ---- where a [rows][32 lanes] float4 table lives ---------------------------------------------------------------------
+// Both policies hand the table to `use(chunk, r)` four rows (16 registers) at a time, in order.
+//   TabMem : shared or global memory, one 128-bit load per row;
+//   TabTmem: tensor memory (row m = columns 4 m .. 4 m + 3 of the thread's lane), one tcgen05.ld per chunk, the next chunk
+//            in flight while the current one is used.
+struct TabMem {
+    const float4* t;
+    int lane;
+    template <int NCH, class F>
+    __device__ __forceinline__ void stream(F&& use) const {
+        static_for<0, NCH>([&](auto cc) {
+            constexpr int c = decltype(cc)::value;
+            uint32_t r[16];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float4 q = t[(4 * c + i) * 32 + lane];
+                r[4 * i] = __float_as_uint(q.x); r[4 * i + 1] = __float_as_uint(q.y); r[4 * i + 2] = __float_as_uint(q.z); r[4 * i + 3] = __float_as_uint(q.w);
+            }
+            use(cc, r);
+        });
+    }
+};
+struct TabTmem {
+    uint32_t base;                                   // lane quadrant | first column
+    template <int NCH, class F>
+    __device__ __forceinline__ void stream(F&& use) const {
+        uint32_t a[16], b[16];
+        tmem_ld16(base, a);
+        static_for<0, NCH>([&](auto cc) {
+            constexpr int c = decltype(cc)::value;
+            if constexpr (c % 2 == 0) {
+                tmem_wait16(a);
+                if constexpr (c + 1 < NCH) tmem_ld16(base + 16 * (c + 1), b);
+                use(cc, a);
+            } else {
+                tmem_wait16(b);
+                if constexpr (c + 1 < NCH) tmem_ld16(base + 16 * (c + 1), a);
+                use(cc, b);
+            }
+        });
+    }
+};
+
 __host__ __device__ constexpr int brev4(int i) { return ((i & 1) << 3) | ((i & 2) << 1) | ((i & 4) >> 1) | ((i & 8) >> 3); }
 
 // (re, im) * exp(-2 pi i J / 32) on pairs, J in 0..15
@@ -109,18 +152,20 @@ __device__ __forceinline__ int pk_col(int n1) { return 2 * (n1 & 15) + (n1 >> 4)
 // in : layout A, element n2 = z[lane + 32 n2] (only the first NZ elements non-zero)
 // out: layout B, element k2 = Z[lane + 32 k2]
 // tw4: [16][32] float4 (c[2m], c[2m+1], s[2m], s[2m+1]) of W1024^(lane k1) = c + i s, k1 = 2m, 2m + 1
-template <int NZ>
-__device__ __forceinline__ void warp_fft1024_pk(Pk& p, float* xs, const float4* __restrict__ tw4, int lane) {
+template <int NZ, class TAB>
+__device__ __forceinline__ void warp_fft1024_pk(Pk& p, float* xs, const TAB& tw4, int lane) {
     constexpr int XS = XsStride<float>::value;
     fft32_ab<NZ>(p);
-    static_for<0, 16>([&](auto mm) {
-        constexpr int m = decltype(mm)::value;
-        const float4 w = tw4[m * 32 + lane];
-        const float2 c = make_float2(w.x, w.y), s = make_float2(w.z, w.w);
-        const float2 nr = __ffma2_rn(p.re[m], c, __fmul2_rn(p.im[m], neg2(s)));
-        const float2 ni = __ffma2_rn(p.re[m], s, __fmul2_rn(p.im[m], c));
-        p.re[m] = nr;
-        p.im[m] = ni;
+    tw4.template stream<4>([&](auto cc, const uint32_t (&r)[16]) {
+        static_for<0, 4>([&](auto ii) {
+            constexpr int m = 4 * decltype(cc)::value + decltype(ii)::value, i = decltype(ii)::value;
+            const float2 c = make_float2(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]));
+            const float2 s = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
+            const float2 nr = __ffma2_rn(p.re[m], c, __fmul2_rn(p.im[m], neg2(s)));
+            const float2 ni = __ffma2_rn(p.re[m], s, __fmul2_rn(p.im[m], c));
+            p.re[m] = nr;
+            p.im[m] = ni;
+        });
     });
     float* col = xs + pk_col(lane);
     const float4* row = reinterpret_cast<const float4*>(xs + lane * XS);
@@ -197,18 +242,20 @@ __device__ __forceinline__ void fft32_ba(Pk& p) {
 
 // The same transform for an input in layout B (first pass = fft32_ba, twiddle on layout-A pairs).
 // tw4a: [16][32] float4 (c[j], c[j + 16], s[j], s[j + 16]) of W1024^(lane k1), k1 = j, j + 16
-template <class F>
-__device__ __forceinline__ void warp_fft1024_pk_b(Pk& p, float* xs, const float4* __restrict__ tw4a, int lane, F&& xs_idle) {
+template <class TAB, class F>
+__device__ __forceinline__ void warp_fft1024_pk_b(Pk& p, float* xs, const TAB& tw4a, int lane, F&& xs_idle) {
     constexpr int XS = XsStride<float>::value;
     fft32_ba(p);
-    static_for<0, 16>([&](auto jj) {
-        constexpr int j = decltype(jj)::value;
-        const float4 w = tw4a[j * 32 + lane];
-        const float2 c = make_float2(w.x, w.y), s = make_float2(w.z, w.w);
-        const float2 nr = __ffma2_rn(p.re[j], c, __fmul2_rn(p.im[j], neg2(s)));
-        const float2 ni = __ffma2_rn(p.re[j], s, __fmul2_rn(p.im[j], c));
-        p.re[j] = nr;
-        p.im[j] = ni;
+    tw4a.template stream<4>([&](auto cc, const uint32_t (&r)[16]) {
+        static_for<0, 4>([&](auto ii) {
+            constexpr int j = 4 * decltype(cc)::value + decltype(ii)::value, i = decltype(ii)::value;
+            const float2 c = make_float2(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]));
+            const float2 s = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
+            const float2 nr = __ffma2_rn(p.re[j], c, __fmul2_rn(p.im[j], neg2(s)));
+            const float2 ni = __ffma2_rn(p.re[j], s, __fmul2_rn(p.im[j], c));
+            p.re[j] = nr;
+            p.im[j] = ni;
+        });
     });
     float* col = xs + pk_col(lane);
     const float4* row = reinterpret_cast<const float4*>(xs + lane * XS);
@@ -249,7 +296,8 @@ constexpr int PK_PARK_PLANE = 33 * PK_PARK_S;             // floats per plane (r
 constexpr int PK_PARK_BYTES = 2 * PK_PARK_PLANE * 4;      // 4752
 
 // wp4: [8][32] float4 (wx[ka0], wx[ka1], wy[ka0], wy[ka1]),  wp2[k] = (wx, wy) = (-sin th, -cos th), th = 2 pi k / 2048
-__device__ __forceinline__ void pk_post_pairs(Pk& p, float* park, const float4* __restrict__ wp4, int lane) {
+template <class TAB>
+__device__ __forceinline__ void pk_post_pairs(Pk& p, float* park, const TAB& wp4, int lane) {
     float* pre = park;
     float* pim = park + PK_PARK_PLANE;
     {
@@ -263,29 +311,33 @@ __device__ __forceinline__ void pk_post_pairs(Pk& p, float* park, const float4* 
     }
     __syncwarp();
     const int rb = lane ? (32 - lane) * PK_PARK_S : 32 * PK_PARK_S;
-    static_for<0, 8>([&](auto mm) {
-        constexpr int m = decltype(mm)::value;
-        const float2 qr = *reinterpret_cast<const float2*>(pre + rb + 2 * m), qi = *reinterpret_cast<const float2*>(pim + rb + 2 * m);
-        const float4 w = wp4[m * 32 + lane];
-        const float2 wx = make_float2(w.x, w.y), wy = make_float2(w.z, w.w);
-        const float2 zr = p.re[m], zi = p.im[m];
-        const float2 er = __fadd2_rn(zr, qr), ei = __fadd2_rn(zi, neg2(qi)), orr = __fadd2_rn(zr, neg2(qr)), oi = __fadd2_rn(zi, qi);
-        const float2 A = __ffma2_rn(wx, orr, __fmul2_rn(neg2(wy), oi)), B = __ffma2_rn(wx, oi, __fmul2_rn(wy, orr));
-        p.re[m] = __fadd2_rn(er, A);
-        p.im[m] = __fadd2_rn(B, ei);
-        p.re[m + 8] = __fadd2_rn(er, neg2(A));
-        p.im[m + 8] = __fadd2_rn(B, neg2(ei));
+    wp4.template stream<2>([&](auto cc, const uint32_t (&r)[16]) {
+        static_for<0, 4>([&](auto ii) {
+            constexpr int m = 4 * decltype(cc)::value + decltype(ii)::value, i = decltype(ii)::value;
+            const float2 qr = *reinterpret_cast<const float2*>(pre + rb + 2 * m), qi = *reinterpret_cast<const float2*>(pim + rb + 2 * m);
+            const float2 wx = make_float2(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]));
+            const float2 wy = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
+            const float2 zr = p.re[m], zi = p.im[m];
+            const float2 er = __fadd2_rn(zr, qr), ei = __fadd2_rn(zi, neg2(qi)), orr = __fadd2_rn(zr, neg2(qr)), oi = __fadd2_rn(zi, qi);
+            const float2 A = __ffma2_rn(wx, orr, __fmul2_rn(neg2(wy), oi)), B = __ffma2_rn(wx, oi, __fmul2_rn(wy, orr));
+            p.re[m] = __fadd2_rn(er, A);
+            p.im[m] = __fadd2_rn(B, ei);
+            p.re[m + 8] = __fadd2_rn(er, neg2(A));
+            p.im[m + 8] = __fadd2_rn(B, neg2(ei));
+        });
     });
 }
 
-__device__ __forceinline__ void pk_pre_pairs(Pk& p, float* park, const float4* __restrict__ wp4, int lane) {
+template <class TAB>
+__device__ __forceinline__ void pk_pre_pairs(Pk& p, float* park, const TAB& wp4, int lane) {
     float* pre = park;
     float* pim = park + PK_PARK_PLANE;
     const int wb = lane ? (32 - lane) * PK_PARK_S : 1;
-    static_for<0, 8>([&](auto mm) {
-        constexpr int m = decltype(mm)::value;
-        const float4 w = wp4[m * 32 + lane];
-        const float2 wx = make_float2(w.x, w.y), wy = make_float2(w.z, w.w);
+    wp4.template stream<2>([&](auto cc, const uint32_t (&r)[16]) {
+      static_for<0, 4>([&](auto ii) {
+        constexpr int m = 4 * decltype(cc)::value + decltype(ii)::value, i = decltype(ii)::value;
+        const float2 wx = make_float2(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]));
+        const float2 wy = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
         const float2 xr = p.re[m], xi = p.im[m], rr = p.re[m + 8], ri = p.im[m + 8];
         const float2 er = __fadd2_rn(xr, rr), ei = __fadd2_rn(xi, neg2(ri)), dr = __fadd2_rn(xr, neg2(rr)), di = __fadd2_rn(xi, ri);
         const float2 C = __ffma2_rn(wx, dr, __fmul2_rn(wy, di));
@@ -295,6 +347,7 @@ __device__ __forceinline__ void pk_pre_pairs(Pk& p, float* park, const float4* _
         const float2 br = __fadd2_rn(er, neg2(C)), bi = __fadd2_rn(ei, nD);   // mirror: (er - C, -(D - ei))
         pre[wb + 15 - 2 * m] = br.x; pre[wb + 14 - 2 * m] = br.y;
         pim[wb + 15 - 2 * m] = bi.x; pim[wb + 14 - 2 * m] = bi.y;
+      });
     });
 }
 // after the caller has dealt with bin 512 and synchronised the warp: elements 16..31 back from the own row

@@ -239,12 +239,41 @@ template <class T> __host__ __device__ constexpr int xs_bytes() { return 32 * Xs
 
 // mid(): called between the two planes, where only the 32 imaginary parts are live in registers -- the cheapest point
 // of the transform for anything that needs registers of its own (e.g. a barrier wait).
-template <class T, int NZ, class MID>
-__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const cplx_t<T>* __restrict__ tw, int lane, MID&& mid) {
+// twiddle sources for warp_fft1024_split: a [k1][lane] table in shared / global memory, or the same table in tensor
+// memory (row k1 = columns 4 k1 .. 4 k1 + 3 of the thread's lane for double2; float2 rows are not used from TMEM)
+template <class T>
+struct TwMem {
+    const cplx_t<T>* tw;
+    int lane;
+    __device__ __forceinline__ void apply(cplx_t<T> (&v)[32]) const {
+        static_for<1, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; v[k1] = cmul(v[k1], tw[k1 * 32 + lane]); });
+    }
+};
+struct TwTmemF64 {
+    uint32_t base;                                   // lane quadrant | column of row 0
+    __device__ __forceinline__ void apply(double2 (&v)[32]) const {
+        static_for<0, 8>([&](auto cc) {
+            constexpr int c = decltype(cc)::value;
+            uint32_t r[16];
+            tmem_ld16(base + 16 * c, r);
+            tmem_wait16(r);
+            static_for<0, 4>([&](auto ii) {
+                constexpr int k1 = 4 * c + decltype(ii)::value, i = decltype(ii)::value;
+                if constexpr (k1 > 0) {
+                    const double wx = __hiloint2double((int)r[4 * i + 1], (int)r[4 * i]), wy = __hiloint2double((int)r[4 * i + 3], (int)r[4 * i + 2]);
+                    v[k1] = cmul(v[k1], make_double2(wx, wy));
+                }
+            });
+        });
+    }
+};
+
+template <class T, int NZ, class TW, class MID>
+__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const TW& tw, int lane, MID&& mid) {
     using C = cplx_t<T>;
     constexpr int XS = XsStride<T>::value;
     fft32<NZ>(v);
-    static_for<1, 32>([&](auto kk) { constexpr int k1 = decltype(kk)::value; v[k1] = cmul(v[k1], tw[k1 * 32 + lane]); });
+    tw.apply(v);
     auto read_row = [&](auto sel) {
         if constexpr (sizeof(T) == 4) {
             const float4* row = reinterpret_cast<const float4*>(xs + lane * XS);
@@ -274,8 +303,8 @@ __device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, co
     fft32<32>(v);
 }
 
-template <class T, int NZ>
-__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const cplx_t<T>* __restrict__ tw, int lane) {
+template <class T, int NZ, class TW>
+__device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const TW& tw, int lane) {
     warp_fft1024_split<T, NZ>(v, xs, tw, lane, []() {});
 }
 

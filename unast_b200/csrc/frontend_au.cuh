@@ -18,6 +18,10 @@
 
 namespace unast {
 
+#ifndef UNAST_FE_TMEM
+#define UNAST_FE_TMEM 1                      // float64 mode: the [k1][lane] twiddle table lives in tensor memory
+#endif
+
 constexpr int AU_ROW = 1032;                 // floats per |X| row: bins 0..1024 + zero padding up to the last item's end
 constexpr int AU_BATCH = 5;                  // rounds per batch; the host pads the tables to a multiple of it
 constexpr int AU_MAX_ROUNDS = 15;
@@ -44,7 +48,7 @@ struct FeAuLayout {
     static constexpr int off_k0 = off_w + AU_MAX_ROUNDS * 64 * 16;
     static constexpr int off_mel = off_k0 + AU_MAX_ROUNDS * 32 * 4;
     static constexpr int off_state = off_mel + NMELS * 8;                // per-warp loop state, 8 words each
-    static constexpr int bytes = off_state + FW * 32;
+    static constexpr int bytes = off_state + FW * 32 + 16;               // + the TMEM base address word
     static_assert(XCH_BYTES >= AU_MAX_ROUNDS * 32 * 4, "partial sums live in the idle exchange buffer");
     static_assert(bytes <= 227 * 1024, "shared memory budget");
 };
@@ -66,7 +70,31 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
     unsigned char* stage = smem + L::off_stage + warp * PF_STAGE_BYTES;
 
     for (int i = tid; i < NLIVE_C; i += NT) s_win[i] = reinterpret_cast<const C*>(P.win2)[i];
-    for (int i = tid; i < 1024; i += NT) s_tw[i] = reinterpret_cast<const C*>(P.tw1024)[i];
+    constexpr bool TW_TMEM = UNAST_FE_TMEM && sizeof(T) == 8;
+    uint32_t tq = 0;
+    if constexpr (TW_TMEM) {
+        // The inter-pass twiddle table W1024^(lane k1) goes to tensor memory (31 complex doubles per lane = columns [0, 128),
+        // one copy per lane quadrant) and is read with tcgen05.ld in the middle of the float64 phase: 35.4 -> 32.3 ms on C2
+        // (profiles/r3_fe_variants.txt).  Moving the window taps and the filterbank weights there as well changed nothing
+        // (32.6 ms): it is the latency of the twiddle loads inside the FP64 critical path that mattered, not the bandwidth.
+        uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::off_state + FW * 32);
+        if (warp == 0) tmem_alloc(s_tmem, 128);
+        tmem_fence_before_sync();
+        __syncthreads();
+        tmem_fence_after_sync();
+        tq = *s_tmem + ((uint32_t)(32 * (warp & 3)) << 16);
+        if (warp < 4) {
+            for (int k1 = 0; k1 < 32; ++k1) {
+                const double2 w = reinterpret_cast<const double2*>(P.tw1024)[k1 * 32 + lane];
+                tmem_st4(tq + 4 * k1, make_float4(__int_as_float(__double2loint(w.x)), __int_as_float(__double2hiint(w.x)),
+                                                  __int_as_float(__double2loint(w.y)), __int_as_float(__double2hiint(w.y))));
+            }
+            tmem_wait_st();
+        }
+        tmem_fence_before_sync();
+    } else {
+        for (int i = tid; i < 1024; i += NT) s_tw[i] = reinterpret_cast<const C*>(P.tw1024)[i];
+    }
     if constexpr (L::WP_TABLE) {
         C* s_wp = reinterpret_cast<C*>(smem + L::off_wp);
         for (int i = tid; i < 1024; i += NT) s_wp[i] = reinterpret_cast<const C*>(P.wp2)[i];
@@ -76,7 +104,8 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
     for (int i = tid; i < rounds * 32; i += NT) s_k0[i] = MI.k0[i];
     for (int i = tid; i < NMELS; i += NT) s_mel[i] = MI.mel[i];
     for (int i = tid; i < FW * AU_ROW; i += NT) reinterpret_cast<float*>(smem + L::off_rows)[i] = 0.0f;   // incl. the padding
-    __syncthreads();                                                      // the only CTA-wide barrier
+    __syncthreads();                                                      // the only CTA-wide barrier of the steady state
+    if constexpr (TW_TMEM) tmem_fence_after_sync();
 
     auto wp = [&]() {
         if constexpr (L::WP_TABLE) return WpTable<T>{reinterpret_cast<const C*>(smem + L::off_wp)};
@@ -87,7 +116,14 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
     const long long F = P.frame_off[P.B];
     const long long NW = (long long)gridDim.x * FW, gw = (long long)blockIdx.x * FW + warp;
     const int fa = (int)(F * gw / NW), fb = (int)(F * (gw + 1) / NW);
-    if (fa >= fb) return;
+    auto release_tmem = [&]() {                                           // tensor memory is released when every warp is done
+        if constexpr (TW_TMEM) {
+            tmem_fence_before_sync();
+            asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");
+            if (warp == 0) tmem_dealloc(*reinterpret_cast<uint32_t*>(smem + L::off_state + FW * 32), 128);
+        }
+    };
+    if (fa >= fb) { release_tmem(); return; }
     int b;
     {   // last b with frame_off[b] <= fa
         int lo = 0, hi = P.B;
@@ -148,7 +184,8 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
             if (f1 < st[1] && f1 < st[2] && prefetched(t + 1)) pf_issue(P.wave, wbase, t + 1, stage, lane);
         }
 
-        warp_fft1024_split<T, 18>(v, xs, s_tw, lane);
+        if constexpr (TW_TMEM) warp_fft1024_split<T, 18>(v, xs, TwTmemF64{tq}, lane);
+        else warp_fft1024_split<T, 18>(v, xs, TwMem<T>{s_tw, lane}, lane);
 
         float* mrow = P.mag_out ? P.mag_out + (size_t)st[0] * NBINS : nullptr;
         {
@@ -222,6 +259,7 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
         if (lane == 0) st[0] = st[0] + 1;
         __syncwarp();
     }
+    release_tmem();
 }
 
 }  // namespace unast

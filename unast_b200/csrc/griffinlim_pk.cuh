@@ -24,13 +24,19 @@
 
 namespace unast {
 
+#ifndef UNAST_GL_TMEM
+#define UNAST_GL_TMEM 1                     // FFT twiddle and post-/pre-processing tables in tensor memory (0: shared memory)
+#endif
+// TMEM columns of the tables (row m of a [rows][32] float4 table = columns 4 m .. 4 m + 3 of the thread's lane)
+constexpr int GLT_TWB = 0, GLT_TWA = 64, GLT_WP4 = 128, GLT_COLS = 256;
+
 constexpr int GLP_XS_BYTES = PK_PARK_BYTES > GL_XS_BYTES ? PK_PARK_BYTES : GL_XS_BYTES;   // 4752: transposition / park buffer
 constexpr int GLP_SROW_BYTES = S_STRIDE * 4;                                               // 4128
 constexpr int GLP_WARP_BYTES = GLP_XS_BYTES + GLP_SROW_BYTES + GL_CARRY * 4;               // 12192
 constexpr int GLP_X_BYTES = (WIN + 6 + 3) / 4 * 16;                                        // 4432: taps + alignment slack
 constexpr int glp_off_warp = 0;
 constexpr int glp_off_bar = glp_off_warp + GL_WARPS * GLP_WARP_BYTES;                      // two mbarriers per warp
-constexpr int glp_off_wa = glp_off_bar + GL_WARPS * 16;
+constexpr int glp_off_wa = glp_off_bar + GL_WARPS * 16 + 16;                                 // + the TMEM base address word
 constexpr int glp_off_win = glp_off_wa + (NLIVE_C * 8 + 15) / 16 * 16;
 constexpr int glp_off_wini = glp_off_win + (NLIVE_C * 8 + 15) / 16 * 16;
 constexpr int glp_off_twb = glp_off_wini + (NLIVE_C * 8 + 15) / 16 * 16;
@@ -123,15 +129,43 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
     float4* s_wp4 = reinterpret_cast<float4*>(smem + glp_off_wp4);
 
     for (int i = tid; i < NLIVE_C; i += NT) { s_wa[i] = P.wa2[i]; s_win[i] = P.win2[i]; s_wini[i] = P.wini2[i]; }
+#if UNAST_GL_TMEM
+    // The three [rows][lane] float4 tables go to tensor memory, one copy per lane quadrant (a warp reaches the 32 lanes of
+    // quadrant warp % 4 only): 192 of the ~890 shared-memory wavefronts per frame move to the tcgen05.ld data path.
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + glp_off_bar + GL_WARPS * 16);
+    if (warp == 0) tmem_alloc(s_tmem, GLT_COLS);
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    const uint32_t tq = *s_tmem + ((uint32_t)(32 * (warp & 3)) << 16);   // this warp's lane quadrant
+    if (warp < 4) {
+        for (int m = 0; m < 16; ++m) { tmem_st4(tq + GLT_TWB + 4 * m, P.tw4[m * 32 + lane]); tmem_st4(tq + GLT_TWA + 4 * m, P.tw4a[m * 32 + lane]); }
+        for (int m = 0; m < 8; ++m) tmem_st4(tq + GLT_WP4 + 4 * m, P.wp4[m * 32 + lane]);
+        tmem_wait_st();
+    }
+    tmem_fence_before_sync();
+    const TabTmem t_twb{tq + GLT_TWB}, t_twa{tq + GLT_TWA}, t_wp4{tq + GLT_WP4};
+#else
     for (int i = tid; i < 512; i += NT) { s_twb[i] = P.tw4[i]; s_twa[i] = P.tw4a[i]; }
     for (int i = tid; i < 256; i += NT) s_wp4[i] = P.wp4[i];
+    const TabMem t_twb{s_twb, lane}, t_twa{s_twa, lane}, t_wp4{s_wp4, lane};
+#endif
     if (lane == 0) { mbar_init(bar_s, 1); mbar_init(bar_x, 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    __syncthreads();                                                    // the only CTA-wide barrier
+    __syncthreads();                                                    // tables, barriers (and tensor memory) are set up
+#if UNAST_GL_TMEM
+    tmem_fence_after_sync();
+#endif
 
     // this warp's run of frames (equal shares of a cost that weights edge frames; resolved once on the host)
     const int gw = blockIdx.x * GL_WARPS + warp;
-    if (gw >= P.n_runs) return;
+    if (gw >= P.n_runs) {
+#if UNAST_GL_TMEM
+        asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");            // tensor memory is released when every warp is done
+        if (warp == 0) tmem_dealloc(*s_tmem, GLT_COLS);
+#endif
+        return;
+    }
     const int cta_threads = 32 * min(GL_WARPS, P.n_runs - blockIdx.x * GL_WARPS);   // warps of this CTA that own a run
     bool dead = false;                                                   // a wait timed out: keep the barriers company, do nothing
     const int4 run = P.runs[gw];
@@ -311,8 +345,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                 }
                 static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; reA<j>(v) = 0.f; imA<j>(v) = 0.f; });
                 // ---- 2. STFT column (layout B out), mirror pairs: pair m = X[ka], pair m + 8 = X[1024 - ka] ----
-                warp_fft1024_pk<18>(v, xs, s_twb, lane);
-                pk_post_pairs(v, xs, s_wp4, lane);
+                warp_fft1024_pk<18>(v, xs, t_twb, lane);
+                pk_post_pairs(v, xs, t_wp4, lane);
             }
             // ---- 3. phase update against S on the mirror pairs: ka = lane + 64 m (+ 32), kb = 1024 - ka ----
             mbar_wait(bar_s, ph_s);                                          // the frame's target-magnitude row has landed
@@ -400,7 +434,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                 }
             }
             // ---- 4. back to Z' (layout B, in place; mirrors through the park buffer), ISTFT column ----
-            pk_pre_pairs(v, xs, s_wp4, lane);
+            pk_pre_pairs(v, xs, t_wp4, lane);
             if (lane == 0) { xs[0] = 2.0f * x512r; xs[PK_PARK_PLANE] = 2.0f * x512i; }   // element 16 of lane 0
             __syncwarp();
             // next frame's S row (this one has been consumed); after the run's last frame, the first row for the next iteration
@@ -410,7 +444,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
             __syncwarp();
             // the next frame's taps go into the transposition buffer as soon as the inverse transform is done with it
             x_staged = iter_mode && f + 1 < f1 && f + 1 < fend && t + 1 >= 4 && t + 1 <= Tb - 5;
-            warp_fft1024_pk_b(v, xs, s_twa, lane, [&]() {
+            warp_fft1024_pk_b(v, xs, t_twa, lane, [&]() {
                 if (x_staged && lane == 0) tma_load_1d(xs, ola_r + ((pos0 + HOP) & ~3LL), GLP_X_BYTES, bar_x);
             });
 
@@ -487,6 +521,11 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
             st_release_gpu(P.done + gw, P.epoch + it + 1);
         }
     }
+#if UNAST_GL_TMEM
+    tmem_fence_before_sync();
+    asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");
+    if (warp == 0) tmem_dealloc(*s_tmem, GLT_COLS);
+#endif
 }
 
 }  // namespace unast

@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(128) debug_rfft_f64_kernel(const float* __rest
         if (j < 17 || n < NLIVE_C) { const float2 q = src[n]; v[j] = mk(0.5 * (double)q.x, 0.5 * (double)q.y); } else v[j] = mk(0.0, 0.0);
     });
     static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; v[j] = mk(0.0, 0.0); });
-    warp_fft1024_split<double, 18>(v, xs, tw, lane);
+    warp_fft1024_split<double, 18>(v, xs, TwMem<double>{tw, lane}, lane);
     float2* dst = out + (size_t)f * NBINS;
     rfft_post_pairs<double>(v, reinterpret_cast<double2*>(xs), WpLane<double>{wp[lane]}, lane, [&](auto jj, double2 xa, double2 xb) {
         constexpr int j = decltype(jj)::value;
@@ -156,8 +156,8 @@ __global__ void __launch_bounds__(128) debug_rfft_pk_kernel(const float* __restr
         if (j < 17 || n < NLIVE_C) { const float2 q = src[n]; reA<j>(v) = 0.5f * q.x; imA<j>(v) = 0.5f * q.y; } else { reA<j>(v) = 0.f; imA<j>(v) = 0.f; }
     });
     static_for<18, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; reA<j>(v) = 0.f; imA<j>(v) = 0.f; });
-    warp_fft1024_pk<18>(v, xs, tw4, lane);
-    pk_post_pairs(v, xs, wp4, lane);
+    warp_fft1024_pk<18>(v, xs, TabMem{tw4, lane}, lane);
+    pk_post_pairs(v, xs, TabMem{wp4, lane}, lane);
     float2* dst = out + (size_t)f * NBINS;
     static_for<0, 8>([&](auto mm) {
         constexpr int m = decltype(mm)::value;
@@ -188,12 +188,12 @@ __global__ void __launch_bounds__(128) debug_irfft_kernel(const float2* __restri
     });
     float2 x512 = make_float2(0.f, 0.f);
     if (lane == 0) { v.im[0].x = 0.f; v.im[8].x = 0.f; x512 = src[512]; }      // irfft ignores Im of DC and Nyquist
-    pk_pre_pairs(v, xs, wp4, lane);
+    pk_pre_pairs(v, xs, TabMem{wp4, lane}, lane);
     if (lane == 0) { xs[0] = 2.0f * x512.x; xs[PK_PARK_PLANE] = 2.0f * x512.y; }
     __syncwarp();
     pk_pre_collect(v, xs, lane);
     __syncwarp();
-    warp_fft1024_pk_b(v, xs, tw4a, lane, []() {});
+    warp_fft1024_pk_b(v, xs, TabMem{tw4a, lane}, lane, []() {});
     float2* dst = reinterpret_cast<float2*>(out + (size_t)f * WIN);
     static_for<0, 18>([&](auto jj) {
         constexpr int j = decltype(jj)::value;

@@ -131,37 +131,47 @@ __global__ void __launch_bounds__(PRE_THREADS, 1) prenet_fc1_kernel(const Prenet
     const uint32_t chunk_stride = (uint32_t)(N / 8) * 128u;                  // bytes between consecutive 16-byte K chunks
     uint32_t ph_d = 0;
 
-    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const long long row = (long long)tile * PRE_TILE_M + tid;            // this thread's row == its TMEM lane
-        const bool valid = row < M;
-        // ---- the masked input row -> A operand in tensor memory (hi, lo) ----
-        float fill = 0.0f, kp = 1.0f;
-        bool masked = false;
-        const float4* xr = nullptr;
-        if (valid) {
-            const int b = (int)(row / P.T), t = (int)(row % P.T);
-            xr = reinterpret_cast<const float4*>(P.x + (size_t)row * PRE_K);
+    // A row in flight: the NEXT tile's row is fetched (20 x 128-bit loads per thread) right after this tile's MMAs have been
+    // issued, so its HBM latency hides behind the tensor cores and the epilogue.
+    struct RowIn { float4 q[PRE_K / 4]; float fill, kp; bool masked, valid; long long row; };
+    auto fetch_row = [&](int tile) {
+        RowIn r;
+        r.row = (long long)tile * PRE_TILE_M + tid;                          // this thread's row == its TMEM lane
+        r.valid = tile < tiles && r.row < M;
+        r.fill = 0.0f; r.kp = 1.0f; r.masked = false;
+        if (r.valid) {
+            const int b = (int)(r.row / P.T), t = (int)(r.row % P.T);
+            const float4* xr = reinterpret_cast<const float4*>(P.x + (size_t)r.row * PRE_K);
+#pragma unroll
+            for (int i = 0; i < PRE_K / 4; ++i) r.q[i] = __ldcs(xr + i);     // streamed once
             if (P.spans) {
                 const int4 sp = reinterpret_cast<const int4*>(P.spans)[b];
-                masked = (t >= sp.x && t < sp.x + sp.y) || (t >= sp.z && t < sp.z + sp.w);
-                if (masked && !P.replace_with_zero) {
+                r.masked = (t >= sp.x && t < sp.x + sp.y) || (t >= sp.z && t < sp.z + sp.w);
+                if (r.masked && !P.replace_with_zero) {
                     double sum = 0.0;
                     for (int q = 0; q < AUG_PARTS; ++q) sum += P.parts[b * AUG_PARTS + q];     // the order aug_apply_kernel uses
-                    fill = (float)(sum / ((double)P.T * PRE_K));
+                    r.fill = (float)(sum / ((double)P.T * PRE_K));
                 }
             }
-            if (P.keep) kp = P.keep[row];
+            if (P.keep) r.kp = P.keep[r.row];
+        } else {
+#pragma unroll
+            for (int i = 0; i < PRE_K / 4; ++i) r.q[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        return r;
+    };
+    RowIn nxt = fetch_row(blockIdx.x);
+
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const RowIn cur = nxt;
+        const long long row = cur.row;
+        const bool valid = cur.valid, masked = cur.masked;
+        const float fill = cur.fill, kp = cur.kp;
+        // ---- the masked input row -> A operand in tensor memory (hi, lo) ----
 #pragma unroll
         for (int c = 0; c < PRE_K / 8; ++c) {                                // 8 features = one K step of the tf32 MMA
-            float v[8];
-            if (valid) {
-                const float4 q0 = xr[2 * c], q1 = xr[2 * c + 1];
-                v[0] = q0.x; v[1] = q0.y; v[2] = q0.z; v[3] = q0.w; v[4] = q1.x; v[5] = q1.y; v[6] = q1.z; v[7] = q1.w;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = 0.0f;
-            }
+            const float4 q0 = cur.q[2 * c], q1 = cur.q[2 * c + 1];
+            const float v[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
             uint32_t hi[8], lo[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -193,6 +203,7 @@ __global__ void __launch_bounds__(PRE_THREADS, 1) prenet_fc1_kernel(const Prenet
                                 idesc_tf32, 1);
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar_d)) : "memory");
         }
+        nxt = fetch_row(tile + gridDim.x);                                   // in flight during the MMAs and the epilogue
         mbar_wait(bar_d, ph_d);
         ph_d ^= 1;
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -210,7 +221,7 @@ __global__ void __launch_bounds__(PRE_THREADS, 1) prenet_fc1_kernel(const Prenet
                     o.z = __uint_as_float(acc[i + 2]) + s_bias[c0 + i + 2];
                     o.w = __uint_as_float(acc[i + 3]) + s_bias[c0 + i + 3];
                     if (P.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-                    *reinterpret_cast<float4*>(yr + c0 + i) = o;
+                    __stcs(reinterpret_cast<float4*>(yr + c0 + i), o);      // written once, not re-read here
                 }
             }
         }

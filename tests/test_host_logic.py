@@ -224,3 +224,48 @@ def test_long_form_chunks_cover_what_their_frames_see():
                 assert c0 == 0 or 275 * a - 552 >= c0
                 assert c1 == n or 275 * (b - 1) + 551 <= c1 - 1
                 assert 1 + (c1 - c0) // 275 >= keep.stop
+
+
+def test_fragment_sample_ranges_tile_the_waveform():
+    """unast_griffinlim_fragment_samples (host-only): the samples the ranks of the sharded long-form Griffin-Lim own are
+    disjoint, ordered and cover [0, 275 (T - 1)) exactly, for every frame_ranges partition."""
+    import ctypes
+    from unast_b200 import _lib
+    from unast_b200.longform import frame_ranges
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    fn = lib.unast_griffinlim_fragment_samples
+    fn.restype = ctypes.c_int
+    fn.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]
+    for T in (48110, 4811, 73, 18):
+        for world in (1, 2, 3, 8):
+            if T // world < 9:
+                continue
+            pos = 0
+            for a, b in frame_ranges(T, world):
+                s, e = ctypes.c_int64(), ctypes.c_int64()
+                assert fn(a, b - a, T, ctypes.byref(s), ctypes.byref(e)) == 0
+                assert s.value == pos and e.value > s.value
+                pos = e.value
+            assert pos == 275 * (T - 1)
+    s, e = ctypes.c_int64(), ctypes.c_int64()
+    assert fn(5, 10, 12, ctypes.byref(s), ctypes.byref(e)) != 0                   # fragment beyond the utterance
+
+
+def test_griffinlim_layout_is_consistent_with_workspace_bytes():
+    """unast_griffinlim_layout (host-only): three rotating buffers of equal size inside the workspace, mailboxes before them."""
+    import ctypes
+    from unast_b200 import _lib
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    lib.unast_griffinlim_layout.restype = ctypes.c_int
+    lib.unast_griffinlim_layout.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_void_p]
+    lib.unast_griffinlim_workspace_bytes.restype = ctypes.c_size_t
+    lib.unast_griffinlim_workspace_bytes.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_float]
+    for frames, mom in (([24055], 0.0), ([100, 9, 4000], 0.99)):
+        fr = np.asarray(frames, np.int32)
+        out = (ctypes.c_size_t * 5)()
+        assert lib.unast_griffinlim_layout(fr.ctypes.data_as(ctypes.c_void_p), fr.size, mom, ctypes.cast(out, ctypes.c_void_p)) == 0
+        o0, o1, o2, mail, total = (int(v) for v in out)
+        pad = int(sum(2048 + 275 * (n - 1) for n in frames)) * 4
+        assert o1 - o0 == o2 - o1 >= pad and mail < o0 and o2 + (o1 - o0) <= total
+        assert total == lib.unast_griffinlim_workspace_bytes(fr.ctypes.data_as(ctypes.c_void_p), fr.size, mom)
+        assert o0 % 256 == 0 and mail % 256 == 0

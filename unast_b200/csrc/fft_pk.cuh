@@ -288,7 +288,7 @@ __device__ __forceinline__ void warp_fft1024_pk_b(Pk& p, float* xs, const TAB& t
 // PK_PARK_S floats; lane l' parks element e >= 16 at row l', slot 31 - e; lane 0 instead at row 32, slot 32 - e, plus
 // its element 0 at slot 0 -- so that every lane reads its two mirrors with one aligned 64-bit load from one base.
 // After pk_post_pairs: pair m = X[ka] (both halves), pair m + 8 = X[kb] of the same two bins' mirrors.
-// pk_pre_pairs takes that back to Z' (conjugated, times 2, see irfft_pre_shfl): own elements in place, the mirrors
+// pk_pre_pairs takes that back to Z' (conjugated, times 2): own elements in place, the mirrors
 // returned through the same rows (only lane l and its mirror lane ever touch row 32 - l), then read back as pairs
 // 8..15.  Lane 0's element 16 (bin 512, its own mirror) is handled by the caller through pk_park_512 / row 0 slot 0.
 constexpr int PK_PARK_S = 18;

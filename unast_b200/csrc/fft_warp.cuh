@@ -8,7 +8,7 @@
 //   pass 1: 32-point FFT over the registers            (fft32, all in registers)
 //   twiddle W1024^(n1 k1) + transpose through shared memory (one exchange per FFT)
 //   pass 2: 32-point FFT over the registers            -> Z[k1 + 32 k2] in lane k1 / register k2
-//   real post-processing pairs bin k with 1024-k through a second shared-memory exchange.
+//   real post-processing pairs bin k with 1024-k (mirrors parked in the idle transposition buffer).
 // The index algebra is validated on the CPU by tools/fft_model.py.
 //
 // Replaces numpy.fft.rfft / irfft as called by librosa.stft / istft on the reference path
@@ -92,46 +92,6 @@ __device__ __forceinline__ void fft32(C (&v)[32]) {
     static_for<0, 32>([&](auto kk) { constexpr int k = decltype(kk)::value; v[k] = t[k]; });
 }
 
-// Row stride (in complex elements) of a warp's exchange buffer: 128-bit reads of a lane's own row are
-// bank-conflict-free for float2 with stride 34 (272 B) and for double2 with stride 33 (528 B).
-template <class T> struct XchStride;
-template <> struct XchStride<float> { static constexpr int value = 34; };
-template <> struct XchStride<double> { static constexpr int value = 33; };
-template <class T> __host__ __device__ constexpr int xch_elems() { return 32 * XchStride<T>::value; }   // >= 1025
-
-// 1024-point complex forward FFT across one warp.
-// in : v[n2] = z[lane + 32 n2]      (only the first NZ registers non-zero)
-// out: v[k2] = Z[lane + 32 k2]
-// tw : [k1][n1] table of W1024^(n1 k1) (shared or global memory)
-template <class T, int NZ>
-__device__ __forceinline__ void warp_fft1024(cplx_t<T> (&v)[32], cplx_t<T>* xch, const cplx_t<T>* __restrict__ tw,
-                                             int lane) {
-    using C = cplx_t<T>;
-    constexpr int XS = XchStride<T>::value;
-    fft32<NZ>(v);
-    static_for<0, 32>([&](auto kk) {
-        constexpr int k1 = decltype(kk)::value;
-        C a = v[k1];
-        if constexpr (k1 > 0) a = cmul(a, tw[k1 * 32 + lane]);
-        xch[k1 * XS + lane] = a;
-    });
-    __syncwarp();
-    if constexpr (sizeof(T) == 4) {
-        const float4* row = reinterpret_cast<const float4*>(xch + lane * XS);
-        static_for<0, 16>([&](auto ii) {
-            constexpr int i = decltype(ii)::value;
-            float4 q = row[i];
-            v[2 * i] = mk((T)q.x, (T)q.y);
-            v[2 * i + 1] = mk((T)q.z, (T)q.w);
-        });
-    } else {
-        const C* row = xch + lane * XS;
-        static_for<0, 32>([&](auto ii) { constexpr int i = decltype(ii)::value; v[i] = row[i]; });
-    }
-    __syncwarp();
-    fft32<32>(v);
-}
-
 // cos(2 pi j / 64), j = 0..16
 constexpr double kCos64[17] = {
     1.0,
@@ -183,55 +143,10 @@ struct WpLane {
     }
 };
 
-// Real-FFT post-processing.  The input frame must have been scaled by 1/2 (folded into the window), i.e.
-// in: v[j] = Z[lane + 32 j] / 2; out: v[j] = X[lane + 32 j], nyq = X[1024] (valid on every lane).
-template <class T, class WP>
-__device__ __forceinline__ void rfft_post(cplx_t<T> (&v)[32], T& nyq, cplx_t<T>* xch, const WP& wp, int lane) {
-    using C = cplx_t<T>;
-    static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; xch[lane + 32 * j] = v[j]; });
-    if (lane == 0) xch[1024] = v[0];
-    __syncwarp();
-    C z0 = xch[0];
-    nyq = (T)2 * (z0.x - z0.y);
-    static_for<0, 32>([&](auto jj) {
-        constexpr int j = decltype(jj)::value;
-        const int k = lane + 32 * j;
-        C z = v[j], p = xch[1024 - k], w = wp.template get<j>(lane);
-        T er = z.x + p.x, ei = z.y - p.y;
-        T orr = z.x - p.x, oi = z.y + p.y;
-        v[j] = mk(fma_t(w.x, orr, fma_t(-w.y, oi, er)), fma_t(w.x, oi, fma_t(w.y, orr, ei)));
-    });
-    __syncwarp();
-}
-
-// Inverse of rfft_post followed by conjugation, i.e. the input of the forward machinery that yields
-// conj(irfft) * 2048.  in: v[j] = X[lane + 32 j], nyq = X[1024]; out: v[j] = 2 conj(Z'[lane + 32 j]).
-template <class T, class WP>
-__device__ __forceinline__ void irfft_pre(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* xch, const WP& wp, int lane) {
-    using C = cplx_t<T>;
-    static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; xch[lane + 32 * j] = v[j]; });
-    if (lane == 0) xch[1024] = mk(nyq, (T)0);
-    __syncwarp();
-    static_for<0, 32>([&](auto jj) {
-        constexpr int j = decltype(jj)::value;
-        const int k = lane + 32 * j;
-        C x = v[j], p = xch[1024 - k], w = wp.template get<j>(lane);
-        T er = x.x + p.x, ei = x.y - p.y;
-        T dr = x.x - p.x, di = x.y + p.y;
-        // 2 Z' = (er, ei) + conj(w) * (dr, di);   conj(w) = (w.x, -w.y)
-        T zr = fma_t(w.x, dr, fma_t(w.y, di, er));
-        T zi = fma_t(w.x, di, fma_t(-w.y, dr, ei));
-        v[j] = mk(zr, -zi);
-    });
-    __syncwarp();
-}
-
-// ---- low-shared-memory variants -------------------------------------------------------------------------
+// ---- the 1024-point complex transform across one warp ---------------------------------------------------
 // warp_fft1024_split transposes the real and the imaginary plane one after the other through a buffer of
-// 32 x XS scalars (float: 4.5 KB, double: 8.5 KB per warp) instead of 32 x XS complex values; the bytes moved are
-// the same.  rfft_post_shfl / irfft_pre_shfl pair bin k with bin 1024 - k by warp shuffles (partner lane
-// (32 - lane) % 32, register 31 - j) instead of a second trip through shared memory; lane 0, whose column pairs
-// with itself (register j <-> 32 - j), goes through a 32-entry side buffer.
+// 32 x XS scalars (float: 4.5 KB, double: 8.5 KB per warp); the real-FFT post-processing on mirror pairs lives in
+// frontend_pf.cuh (rfft_post_pairs) and fft_pk.cuh (pk_post_pairs / pk_pre_pairs).
 template <class T> struct XsStride;
 template <> struct XsStride<float> { static constexpr int value = 36; };    // 144 B rows: conflict-free 128-bit reads
 template <> struct XsStride<double> { static constexpr int value = 34; };   // 272 B rows
@@ -306,72 +221,6 @@ __device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, co
 template <class T, int NZ, class TW>
 __device__ __forceinline__ void warp_fft1024_split(cplx_t<T> (&v)[32], T* xs, const TW& tw, int lane) {
     warp_fft1024_split<T, NZ>(v, xs, tw, lane, []() {});
-}
-
-__device__ __forceinline__ float2 shfl_c(float2 a, int src) {
-    return make_float2(__shfl_sync(0xffffffffu, a.x, src), __shfl_sync(0xffffffffu, a.y, src));
-}
-__device__ __forceinline__ double2 shfl_c(double2 a, int src) {
-    return make_double2(__shfl_sync(0xffffffffu, a.x, src), __shfl_sync(0xffffffffu, a.y, src));
-}
-
-// in: v[j] = Z[lane + 32 j] / 2; out: v[j] = X[lane + 32 j]; nyq = X[1024], valid on lane 0 only.
-// side: 32 complex values of scratch shared memory private to the warp.
-template <class T, class WP>
-__device__ __forceinline__ void rfft_post_shfl(cplx_t<T> (&v)[32], T& nyq, cplx_t<T>* side, const WP& wp, int lane) {
-    using C = cplx_t<T>;
-    const int src = (32 - lane) & 31;
-    const bool l0 = lane == 0;
-    if (l0) static_for<0, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; side[j] = v[j]; });
-    __syncwarp();
-    nyq = (T)2 * (v[0].x - v[0].y);
-    auto one = [&](C z, C p, C w) {
-        T er = z.x + p.x, ei = z.y - p.y;
-        T orr = z.x - p.x, oi = z.y + p.y;
-        return mk(fma_t(w.x, orr, fma_t(-w.y, oi, er)), fma_t(w.x, oi, fma_t(w.y, orr, ei)));
-    };
-    static_for<0, 16>([&](auto jj) {
-        constexpr int j = decltype(jj)::value;
-        C pa = shfl_c(v[31 - j], src);               // partner of register j
-        C pb = shfl_c(v[j], src);                    // partner of register 31 - j
-        if (l0) { pa = side[(32 - j) & 31]; pb = side[j + 1]; }
-        const C a = one(v[j], pa, wp.template get<j>(lane));
-        const C b = one(v[31 - j], pb, wp.template get<31 - j>(lane));
-        v[j] = a;
-        v[31 - j] = b;
-    });
-    __syncwarp();
-}
-
-// in: v[j] = X[lane + 32 j], nyq = X[1024] (read on lane 0); out: v[j] = 2 conj(Z'[lane + 32 j]).
-template <class T, class WP>
-__device__ __forceinline__ void irfft_pre_shfl(cplx_t<T> (&v)[32], T nyq, cplx_t<T>* side, const WP& wp, int lane) {
-    using C = cplx_t<T>;
-    const int src = (32 - lane) & 31;
-    const bool l0 = lane == 0;
-    if (l0) {
-        side[0] = mk(nyq, (T)0);                     // partner of bin 0 is the Nyquist bin
-        static_for<1, 32>([&](auto jj) { constexpr int j = decltype(jj)::value; side[j] = v[j]; });
-    }
-    __syncwarp();
-    auto one = [&](C x, C p, C w) {
-        T er = x.x + p.x, ei = x.y - p.y;
-        T dr = x.x - p.x, di = x.y + p.y;
-        T zr = fma_t(w.x, dr, fma_t(w.y, di, er));
-        T zi = fma_t(w.x, di, fma_t(-w.y, dr, ei));
-        return mk(zr, -zi);
-    };
-    static_for<0, 16>([&](auto jj) {
-        constexpr int j = decltype(jj)::value;
-        C pa = shfl_c(v[31 - j], src);
-        C pb = shfl_c(v[j], src);
-        if (l0) { pa = side[(32 - j) & 31]; pb = side[j + 1]; }
-        const C a = one(v[j], pa, wp.template get<j>(lane));
-        const C b = one(v[31 - j], pb, wp.template get<31 - j>(lane));
-        v[j] = a;
-        v[31 - j] = b;
-    });
-    __syncwarp();
 }
 
 }  // namespace unast

@@ -24,9 +24,6 @@
 
 namespace unast {
 
-#ifndef UNAST_GL_TMEM
-#define UNAST_GL_TMEM 1                     // FFT twiddle and post-/pre-processing tables in tensor memory (0: shared memory)
-#endif
 // TMEM columns of the tables (row m of a [rows][32] float4 table = columns 4 m .. 4 m + 3 of the thread's lane)
 constexpr int GLT_TWB = 0, GLT_TWA = 64, GLT_WP4 = 128, GLT_COLS = 256;
 
@@ -39,10 +36,7 @@ constexpr int glp_off_bar = glp_off_warp + GL_WARPS * GLP_WARP_BYTES;           
 constexpr int glp_off_wa = glp_off_bar + GL_WARPS * 16 + 16;                                 // + the TMEM base address word
 constexpr int glp_off_win = glp_off_wa + (NLIVE_C * 8 + 15) / 16 * 16;
 constexpr int glp_off_wini = glp_off_win + (NLIVE_C * 8 + 15) / 16 * 16;
-constexpr int glp_off_twb = glp_off_wini + (NLIVE_C * 8 + 15) / 16 * 16;
-constexpr int glp_off_twa = glp_off_twb + 512 * 16;
-constexpr int glp_off_wp4 = glp_off_twa + 512 * 16;
-constexpr int glp_smem_bytes = glp_off_wp4 + 256 * 16;
+constexpr int glp_smem_bytes = glp_off_wini + (NLIVE_C * 8 + 15) / 16 * 16;
 static_assert(GLP_XS_BYTES % 16 == 0 && GLP_SROW_BYTES % 16 == 0 && GLP_WARP_BYTES % 16 == 0 && GLP_X_BYTES <= GLP_XS_BYTES &&
               glp_smem_bytes <= 227 * 1024, "shared memory layout");
 
@@ -124,12 +118,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
     float2* s_wa = reinterpret_cast<float2*>(smem + glp_off_wa);
     float2* s_win = reinterpret_cast<float2*>(smem + glp_off_win);
     float2* s_wini = reinterpret_cast<float2*>(smem + glp_off_wini);
-    float4* s_twb = reinterpret_cast<float4*>(smem + glp_off_twb);
-    float4* s_twa = reinterpret_cast<float4*>(smem + glp_off_twa);
-    float4* s_wp4 = reinterpret_cast<float4*>(smem + glp_off_wp4);
 
     for (int i = tid; i < NLIVE_C; i += NT) { s_wa[i] = P.wa2[i]; s_win[i] = P.win2[i]; s_wini[i] = P.wini2[i]; }
-#if UNAST_GL_TMEM
     // The three [rows][lane] float4 tables go to tensor memory, one copy per lane quadrant (a warp reaches the 32 lanes of
     // quadrant warp % 4 only): 192 of the ~890 shared-memory wavefronts per frame move to the tcgen05.ld data path.
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + glp_off_bar + GL_WARPS * 16);
@@ -145,25 +135,16 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
     }
     tmem_fence_before_sync();
     const TabTmem t_twb{tq + GLT_TWB}, t_twa{tq + GLT_TWA}, t_wp4{tq + GLT_WP4};
-#else
-    for (int i = tid; i < 512; i += NT) { s_twb[i] = P.tw4[i]; s_twa[i] = P.tw4a[i]; }
-    for (int i = tid; i < 256; i += NT) s_wp4[i] = P.wp4[i];
-    const TabMem t_twb{s_twb, lane}, t_twa{s_twa, lane}, t_wp4{s_wp4, lane};
-#endif
     if (lane == 0) { mbar_init(bar_s, 1); mbar_init(bar_x, 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    __syncthreads();                                                    // tables, barriers (and tensor memory) are set up
-#if UNAST_GL_TMEM
+    __syncthreads();                                                    // tables, barriers and tensor memory are set up
     tmem_fence_after_sync();
-#endif
 
     // this warp's run of frames (equal shares of a cost that weights edge frames; resolved once on the host)
     const int gw = blockIdx.x * GL_WARPS + warp;
     if (gw >= P.n_runs) {
-#if UNAST_GL_TMEM
         asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");            // tensor memory is released when every warp is done
         if (warp == 0) tmem_dealloc(*s_tmem, GLT_COLS);
-#endif
         return;
     }
     const int cta_threads = 32 * min(GL_WARPS, P.n_runs - blockIdx.x * GL_WARPS);   // warps of this CTA that own a run
@@ -521,11 +502,9 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
             st_release_gpu(P.done + gw, P.epoch + it + 1);
         }
     }
-#if UNAST_GL_TMEM
     tmem_fence_before_sync();
     asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");
     if (warp == 0) tmem_dealloc(*s_tmem, GLT_COLS);
-#endif
 }
 
 }  // namespace unast

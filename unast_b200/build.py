@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libunast_spectral.so")
 SOURCES = ["unast_spectral.cu"]
-HEADERS = ["common.cuh", "fft_warp.cuh", "fft_pk.cuh", "frontend.cuh", "frontend_pf.cuh", "frontend_au.cuh", "griffinlim.cuh", "griffinlim_pk.cuh", "trim.cuh", "augment.cuh",
+HEADERS = ["common.cuh", "fft_warp.cuh", "fft_pk.cuh", "frontend.cuh", "frontend_pf.cuh", "frontend_au.cuh", "griffinlim.cuh", "griffinlim_pk.cuh", "trim.cuh", "augment.cuh", "prenet.cuh",
            os.path.join("..", "..", "include", "unast_spectral.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-shared", "-Xcompiler", "-fPIC"]

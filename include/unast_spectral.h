@@ -173,7 +173,7 @@ int unast_mel_augment(unast_ctx* ctx, const float* x, int B, int T, int D, const
  * ReLU), on the tensor cores (tcgen05.mma, A operand in tensor memory, float32 fidelity by operand splitting):
  *     y[b][t][:] = relu(W ((t in a span ? fill_b : x[b][t][:]) * keep[b][t]) + bias)          x: [B][T][80], y: [B][T][n_out]
  * unast_prenet_pack turns nn.Linear's weight [n_out][80] (+ bias [n_out] or NULL) into the image the kernel keeps in shared
- * memory (unast_prenet_packed_bytes(n_out) bytes, device, 16-byte aligned; n_out a multiple of 16, <= 256); repack after
+ * memory (unast_prenet_packed_bytes(n_out) bytes, device, 16-byte aligned; n_out a multiple of 32, <= 256); repack after
  * every weight update.  spans / keep / replace_with_zero as in unast_mel_augment; relu = 0 returns the pre-activation.
  * Dropout (module.py:96) is left to the caller.  workspace >= unast_mel_augment_workspace_bytes(B). */
 size_t unast_prenet_packed_bytes(int n_out);

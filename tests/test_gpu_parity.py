@@ -678,7 +678,7 @@ def test_prenet_fc1_on_tensor_cores_matches_float32_torch(engine):
     torch = _torch()
     torch.backends.cuda.matmul.allow_tf32 = False
     rng = np.random.RandomState(12)
-    for (B, T, N) in ((5, 333, 256), (3, 129, 128), (1, 7, 256)):
+    for (B, T, N) in ((5, 333, 256), (3, 129, 128), (1, 7, 256), (2, 300, 96), (2, 70, 32), (41, 1003, 256)):   # the last: 3 tiles per CTA
         x = torch.from_numpy(rng.uniform(0, 1, size=(B, T, 80)).astype(np.float32)).cuda()
         W = torch.from_numpy((rng.randn(N, 80) / 9).astype(np.float32)).cuda()
         bias = torch.from_numpy(rng.randn(N).astype(np.float32)).cuda()

@@ -4,14 +4,16 @@
 //     ->  fc1 = Linear(num_mels = 80 -> s_pre_hid) + bias  ->  ReLU          (src/module.py:93-95, :109)
 //   y[b][t][:] = relu(W ((t in a span ? fill_b : x[b][t][:]) * keep[b][t]) + bias)
 //
-// This one IS GEMM-shaped ([B T, 80] x [80, N], N = 256 or 128), so it runs on the 5th-generation tensor cores:
-//   * one thread per row builds the masked row and writes it straight into TENSOR MEMORY as the A operand
-//     (tcgen05.st 32x32b: thread i of warp w <-> TMEM lane 32 w + i, K along the columns) -- A never touches shared memory;
+// This one IS GEMM-shaped ([B T, 80] x [80, N], N a multiple of 32 up to 256), so it runs on the 5th-generation tensor cores:
+//   * the rows of a tile arrive by TMA (one 320-byte bulk copy per row, a tile ahead); one thread per row builds the masked
+//     row and writes it straight into TENSOR MEMORY as the A operand (tcgen05.st 32x32b: thread i <-> TMEM lane i of its
+//     quadrant, K along the columns) -- A never exists in shared memory in operand form;
 //   * W sits in shared memory for the whole kernel in the canonical K-major, no-swizzle core-matrix layout (packed once per
 //     weight update by prenet_pack_kernel, brought in by one TMA bulk copy);
-//   * one elected thread issues tcgen05.mma (M = 128, N, K = 8 per instruction) into a TMEM accumulator, signals an
-//     mbarrier through tcgen05.commit, and the same 128 threads read the accumulator back with tcgen05.ld, add the bias,
-//     apply the ReLU and store the row.
+//   * one elected thread issues tcgen05.mma (M = 128, K = 8 per instruction) into a TMEM accumulator split in two column
+//     halves, each signalling its own mbarrier through tcgen05.commit, so that the tensor cores always work under the
+//     epilogue of the other half; the epilogue reads the accumulator with tcgen05.ld.16x256b, adds the bias, applies the
+//     ReLU and stores full sectors.
 // float32 fidelity (the reference's nn.Linear is float32, TF32 off by default) comes from an operand split:
 //     x = xh + xl,  w = wh + wl  (xh, wh: TF32 = top 19 bits; xl, wl: exact remainders)
 //     y = xh wh + xl wh + xh wl      (three kind::tf32 products per K step; the missing xl wl term is 2^-22 |x||w|)
@@ -25,7 +27,7 @@ namespace unast {
 constexpr int PRE_K = NMELS;                       // 80 input features
 constexpr int PRE_MAXN = 256;
 constexpr int PRE_TILE_M = 128;
-constexpr int PRE_THREADS = 128;
+constexpr int PRE_THREADS = 256;                     // two warps per TMEM lane quadrant
 // TMEM columns: accumulator [0, 256), A hi [256, 336), A lo [336, 416)
 constexpr int PRE_COL_D = 0, PRE_COL_AH = 256, PRE_COL_AL = 336;
 
@@ -84,35 +86,58 @@ __device__ __forceinline__ void pre_tmem_st8(uint32_t taddr, const uint32_t (&v)
                  ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
                  : "memory");
 }
-__device__ __forceinline__ void pre_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-    // load and wait in ONE statement: the registers may only be read after tcgen05.wait::ld
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n\t"
-                 "tcgen05.wait::ld.sync.aligned;"
+// 16 lanes x 256 bits, four times along the columns: thread t of the warp receives, for repetition j,
+//   v[4j], v[4j+1] = lane (t / 4),     columns 8 j + 2 (t % 4), + 1        (the m16n8 accumulator fragment)
+//   v[4j+2], v[4j+3] = lane (t / 4) + 8, same columns
+// The registers may only be read after tmem_wait16 on the same array.
+__device__ __forceinline__ void pre_tmem_ld_16x256b_x4(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
                    "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                 : "r"(taddr)
-                 : "memory");
+                 : "r"(taddr));
 }
 
+// Shared memory: [W hi | W lo | bias] [7 mbarriers + the TMEM base word] [input stage: one padded row per TMEM lane].
+// The pad makes one-row-per-lane 128-bit reads conflict-free.
+constexpr int PRE_XROW_BYTES = PRE_K * 4 + 16;                 // 336
+__host__ __device__ constexpr int pre_off_bar(int N) { return (pre_packed_bytes(N) + 15) & ~15; }
+__host__ __device__ constexpr int pre_off_xin(int N) { return pre_off_bar(N) + 64; }
+__host__ __device__ constexpr int pre_smem_bytes(int N) { return pre_off_xin(N) + PRE_TILE_M * PRE_XROW_BYTES; }
+static_assert(pre_smem_bytes(PRE_MAXN) <= 227 * 1024, "shared memory layout");
+
+// Pipeline of one CTA (128 rows = 128 TMEM lanes; 8 warps, warps q and q + 4 share lane quadrant q), tile after tile:
+//   * input: a lane of warps 0-3 fetches ITS row of the next tile with one 320-byte TMA bulk copy (one mbarrier per
+//     quadrant) as soon as the current tile's A operand is complete -- no registers held, full sectors from HBM;
+//   * A operand: the two warps of a quadrant convert five of the ten K steps each;
+//   * the accumulator is split in two column halves with one mbarrier each: while the tensor cores run half 1 of a tile the
+//     threads drain half 0, and half 0 of the NEXT tile runs while they drain half 1;
+//   * output: the two warps of a quadrant drain 16 rows each with tcgen05.ld.16x256b -- a row's 8 columns arrive spread over
+//     four lanes, so every store instruction writes eight full 32-byte sectors, with no shared-memory transposition.
 __global__ void __launch_bounds__(PRE_THREADS, 1) prenet_fc1_kernel(const PrenetParams P) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    const int tid = threadIdx.x, warp = tid >> 5;
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q = warp & 3, g = warp >> 2;                                   // lane quadrant, half of the quadrant's work
     const int N = P.N;
+    const int N0 = ((N / 32 + 1) / 2) * 32, N1 = N - N0;                   // the two accumulator halves (N1 may be 0)
     const int wh_bytes = pre_wh_bytes(N), wl_bytes = pre_wl_bytes(N);
     unsigned char* s_wh = smem;
     unsigned char* s_wl = smem + wh_bytes;
     const float* s_bias = reinterpret_cast<const float*>(smem + wh_bytes + wl_bytes);
-    uint64_t* bar_w = reinterpret_cast<uint64_t*>(smem + ((pre_packed_bytes(N) + 15) & ~15));     // weights landed
-    uint64_t* bar_d = bar_w + 1;                                                                     // accumulator complete
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_w + 2);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + pre_off_bar(N));
+    uint64_t* bar_w = bars;                                                  // weights landed
+    uint64_t* bar_d0 = bars + 1;                                             // accumulator half 0 complete
+    uint64_t* bar_d1 = bars + 2;                                             // accumulator half 1 complete (all MMAs of the tile)
+    uint64_t* bar_x = bars + 3 + q;                                          // this quadrant's 32 input rows landed
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 7);
+    const int trow = 32 * q + lane;                                          // this thread's row of the tile == its TMEM lane
+    unsigned char* xrow = smem + pre_off_xin(N) + trow * PRE_XROW_BYTES;
 
     const long long M = (long long)P.B * P.T;
     const int tiles = (int)((M + PRE_TILE_M - 1) / PRE_TILE_M);
     if ((int)blockIdx.x >= tiles) return;
 
     if (tid == 0) {
-        mbar_init(bar_w, 1);
-        mbar_init(bar_d, 1);
+        for (int i = 0; i < 7; ++i) mbar_init(bars + i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         tma_load_1d(smem, P.packed, (uint32_t)pre_packed_bytes(N), bar_w);   // W hi, W lo, bias: one bulk copy
     }
@@ -124,112 +149,166 @@ __global__ void __launch_bounds__(PRE_THREADS, 1) prenet_fc1_kernel(const Prenet
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tbase = *s_tmem;
-    const uint32_t t_lane = tbase + ((uint32_t)(32 * warp) << 16);           // this warp's 32 lanes of tensor memory
-    mbar_wait(bar_w, 0);
+    const uint32_t t_lane = tbase + ((uint32_t)(32 * q) << 16);              // the quadrant's 32 lanes, one per thread (32x32b)
+    const uint32_t t_epi = tbase + ((uint32_t)(32 * q + 16 * g) << 16);      // the 16 lanes this warp drains (16x256b)
 
-    const uint32_t idesc_tf32 = pre_idesc(2, N);
     const uint32_t chunk_stride = (uint32_t)(N / 8) * 128u;                  // bytes between consecutive 16-byte K chunks
-    uint32_t ph_d = 0;
 
-    // A row in flight: the NEXT tile's row is fetched (20 x 128-bit loads per thread) right after this tile's MMAs have been
-    // issued, so its HBM latency hides behind the tensor cores and the epilogue.
-    struct RowIn { float4 q[PRE_K / 4]; float fill, kp; bool masked, valid; long long row; };
-    auto fetch_row = [&](int tile) {
-        RowIn r;
-        r.row = (long long)tile * PRE_TILE_M + tid;                          // this thread's row == its TMEM lane
-        r.valid = tile < tiles && r.row < M;
+    // ---- input: this lane's row of `tile` -> its padded slot (called by warps 0-3 after the barrier that follows the
+    // last read of the slot's previous contents) ----
+    auto issue_rows = [&](int tile) {
+        if (tile >= tiles) return;
+        const long long base = (long long)tile * PRE_TILE_M + 32 * q;
+        const int nv = (int)max(0LL, min(32LL, M - base));
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (lane == 0)
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar_x)), "r"(nv * PRE_K * 4) : "memory");
+        __syncwarp();
+        if (lane < nv)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(smem_u32(xrow)), "l"(P.x + (size_t)(base + lane) * PRE_K), "r"(PRE_K * 4), "r"(smem_u32(bar_x))
+                         : "memory");
+    };
+    // what the masking ops do to this thread's row of `tile` (fetched one tile ahead)
+    struct RowMask { float fill, kp; bool masked, valid; };
+    auto row_mask = [&](int tile) {
+        RowMask r;
+        const long long row = (long long)tile * PRE_TILE_M + trow;
+        r.valid = tile < tiles && row < M;
         r.fill = 0.0f; r.kp = 1.0f; r.masked = false;
         if (r.valid) {
-            const int b = (int)(r.row / P.T), t = (int)(r.row % P.T);
-            const float4* xr = reinterpret_cast<const float4*>(P.x + (size_t)r.row * PRE_K);
-#pragma unroll
-            for (int i = 0; i < PRE_K / 4; ++i) r.q[i] = __ldcs(xr + i);     // streamed once
+            const int b = (int)(row / P.T), t = (int)(row % P.T);
             if (P.spans) {
                 const int4 sp = reinterpret_cast<const int4*>(P.spans)[b];
                 r.masked = (t >= sp.x && t < sp.x + sp.y) || (t >= sp.z && t < sp.z + sp.w);
                 if (r.masked && !P.replace_with_zero) {
                     double sum = 0.0;
-                    for (int q = 0; q < AUG_PARTS; ++q) sum += P.parts[b * AUG_PARTS + q];     // the order aug_apply_kernel uses
+                    for (int i = 0; i < AUG_PARTS; ++i) sum += P.parts[b * AUG_PARTS + i];     // the order aug_apply_kernel uses
                     r.fill = (float)(sum / ((double)P.T * PRE_K));
                 }
             }
-            if (P.keep) r.kp = P.keep[r.row];
-        } else {
-#pragma unroll
-            for (int i = 0; i < PRE_K / 4; ++i) r.q[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (P.keep) r.kp = P.keep[row];
         }
         return r;
     };
-    RowIn nxt = fetch_row(blockIdx.x);
-
-    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const RowIn cur = nxt;
-        const long long row = cur.row;
-        const bool valid = cur.valid, masked = cur.masked;
-        const float fill = cur.fill, kp = cur.kp;
-        // ---- the masked input row -> A operand in tensor memory (hi, lo) ----
+    // ---- one thread issues the 30 MMAs of an accumulator half; tcgen05.commit arrives on `bar` when they are done ----
+    auto mma_half = [&](int n0, int nn, uint64_t* bar) {
+        const uint32_t idesc = pre_idesc(2, nn);
+        const uint32_t boff = (uint32_t)(n0 / 8) * 128u;                     // first core-matrix row group of the half
+        const uint32_t wh = smem_u32(s_wh) + boff, wl = smem_u32(s_wl) + boff;
+        const uint32_t d = tbase + PRE_COL_D + n0;
+#pragma unroll 1
+        for (int s = 0; s < PRE_K / 8; ++s)                                  // xh wh
+            pre_mma_tf32_ts(d, tbase + PRE_COL_AH + 8 * s, pre_smem_desc(wh + 2 * s * chunk_stride, chunk_stride, 128), idesc, s > 0);
+#pragma unroll 1
+        for (int s = 0; s < PRE_K / 8; ++s)                                  // xl wh
+            pre_mma_tf32_ts(d, tbase + PRE_COL_AL + 8 * s, pre_smem_desc(wh + 2 * s * chunk_stride, chunk_stride, 128), idesc, 1);
+#pragma unroll 1
+        for (int s = 0; s < PRE_K / 8; ++s)                                  // xh wl
+            pre_mma_tf32_ts(d, tbase + PRE_COL_AH + 8 * s, pre_smem_desc(wl + 2 * s * chunk_stride, chunk_stride, 128), idesc, 1);
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+    };
+    // ---- epilogue of accumulator columns [cb, cb + nc) for this warp's 16 rows: + bias -> ReLU -> y; the next 32 columns
+    // are in flight from tensor memory while the current ones are stored ----
+    auto epilogue = [&](int tile, int cb, int nc) {
+        const long long r0 = (long long)tile * PRE_TILE_M + 32 * q + 16 * g + (lane >> 2), r1 = r0 + 8;
+        const int cl = 2 * (lane & 3);
+        const bool v0 = r0 < M, v1 = r1 < M;
+        float* y0 = P.y + (size_t)(v0 ? r0 : 0) * N + cl;
+        float* y1 = P.y + (size_t)(v1 ? r1 : 0) * N + cl;
+        auto put = [&](const uint32_t (&v)[16], int c0) {
 #pragma unroll
-        for (int c = 0; c < PRE_K / 8; ++c) {                                // 8 features = one K step of the tf32 MMA
-            const float4 q0 = cur.q[2 * c], q1 = cur.q[2 * c + 1];
+            for (int j = 0; j < 4; ++j) {
+                const float2 bv = *reinterpret_cast<const float2*>(s_bias + c0 + 8 * j + cl);
+                float2 o0 = make_float2(__uint_as_float(v[4 * j]) + bv.x, __uint_as_float(v[4 * j + 1]) + bv.y);
+                float2 o1 = make_float2(__uint_as_float(v[4 * j + 2]) + bv.x, __uint_as_float(v[4 * j + 3]) + bv.y);
+                if (P.relu) { o0.x = fmaxf(o0.x, 0.f); o0.y = fmaxf(o0.y, 0.f); o1.x = fmaxf(o1.x, 0.f); o1.y = fmaxf(o1.y, 0.f); }
+                if (v0) __stcs(reinterpret_cast<float2*>(y0 + c0 + 8 * j), o0);                  // written once, not re-read here
+                if (v1) __stcs(reinterpret_cast<float2*>(y1 + c0 + 8 * j), o1);
+            }
+        };
+        const int ce = cb + nc;
+        uint32_t va[16], vb[16];
+        pre_tmem_ld_16x256b_x4(t_epi + PRE_COL_D + cb, va);
+        for (int c0 = cb; c0 < ce; c0 += 64) {
+            tmem_wait16(va);
+            if (c0 + 32 < ce) pre_tmem_ld_16x256b_x4(t_epi + PRE_COL_D + c0 + 32, vb);
+            put(va, c0);
+            if (c0 + 32 < ce) {
+                tmem_wait16(vb);
+                if (c0 + 64 < ce) pre_tmem_ld_16x256b_x4(t_epi + PRE_COL_D + c0 + 64, va);
+                put(vb, c0 + 32);
+            }
+        }
+    };
+
+    int tile = blockIdx.x, prev_tile = -1;
+    if (g == 0) issue_rows(tile);
+    RowMask cur = row_mask(tile);
+    uint32_t ph_x = 0, ph_d0 = 0, ph_d1 = 0;
+    mbar_wait(bar_w, 0);
+
+    for (; tile < tiles; tile += gridDim.x) {
+        mbar_wait(bar_x, ph_x);
+        ph_x ^= 1;
+        if (prev_tile >= 0 && N1 > 0) {                                      // the previous tile's MMAs are done: A may be overwritten
+            mbar_wait(bar_d1, ph_d1);
+            ph_d1 ^= 1;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        // ---- the masked input row -> A operand in tensor memory (hi, lo); K steps 5 g .. 5 g + 4 ----
+#pragma unroll
+        for (int cc = 0; cc < PRE_K / 16; ++cc) {                            // 8 features = one K step of the tf32 MMA
+            const int c = (PRE_K / 16) * g + cc;
+            float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
+            if (cur.valid) {
+                q0 = *reinterpret_cast<const float4*>(xrow + 32 * c);
+                q1 = *reinterpret_cast<const float4*>(xrow + 32 * c + 16);
+            }
             const float v[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
             uint32_t hi[8], lo[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const float a = (masked ? fill : v[i]) * kp;                 // aug_apply_kernel's arithmetic: one float32 product
+                const float a = (cur.masked ? cur.fill : v[i]) * cur.kp;     // aug_apply_kernel's arithmetic: one float32 product
                 hi[i] = __float_as_uint(a) & 0xffffe000u;
                 lo[i] = __float_as_uint(a - __uint_as_float(hi[i]));
             }
             pre_tmem_st8(t_lane + PRE_COL_AH + 8 * c, hi);
             pre_tmem_st8(t_lane + PRE_COL_AL + 8 * c, lo);
         }
+        const int next = tile + gridDim.x;
+        const RowMask nxt = row_mask(next);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
-        // ---- one thread issues the 30 MMAs of the tile; tcgen05.commit arrives on bar_d when they are done ----
+        __syncthreads();                                                     // A complete, input rows consumed; half 0 of the previous tile drained
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t wh = smem_u32(s_wh), wl = smem_u32(s_wl);
-#pragma unroll 1
-            for (int s = 0; s < PRE_K / 8; ++s)                              // xh wh
-                pre_mma_tf32_ts(tbase + PRE_COL_D, tbase + PRE_COL_AH + 8 * s, pre_smem_desc(wh + 2 * s * chunk_stride, chunk_stride, 128),
-                                idesc_tf32, s > 0);
-#pragma unroll 1
-            for (int s = 0; s < PRE_K / 8; ++s)                              // xl wh
-                pre_mma_tf32_ts(tbase + PRE_COL_D, tbase + PRE_COL_AL + 8 * s, pre_smem_desc(wh + 2 * s * chunk_stride, chunk_stride, 128),
-                                idesc_tf32, 1);
-#pragma unroll 1
-            for (int s = 0; s < PRE_K / 8; ++s)                              // xh wl
-                pre_mma_tf32_ts(tbase + PRE_COL_D, tbase + PRE_COL_AH + 8 * s, pre_smem_desc(wl + 2 * s * chunk_stride, chunk_stride, 128),
-                                idesc_tf32, 1);
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar_d)) : "memory");
+            mma_half(0, N0, bar_d0);
         }
-        nxt = fetch_row(tile + gridDim.x);                                   // in flight during the MMAs and the epilogue
-        mbar_wait(bar_d, ph_d);
-        ph_d ^= 1;
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // ---- epilogue: accumulator row -> + bias -> ReLU -> y[row][:] ----
-        float* yr = P.y + (size_t)(valid ? row : 0) * N;
-        for (int c0 = 0; c0 < N; c0 += 16) {
-            uint32_t acc[16];
-            pre_tmem_ld16(t_lane + PRE_COL_D + c0, acc);
-            if (valid) {
-#pragma unroll
-                for (int i = 0; i < 16; i += 4) {
-                    float4 o;
-                    o.x = __uint_as_float(acc[i]) + s_bias[c0 + i];
-                    o.y = __uint_as_float(acc[i + 1]) + s_bias[c0 + i + 1];
-                    o.z = __uint_as_float(acc[i + 2]) + s_bias[c0 + i + 2];
-                    o.w = __uint_as_float(acc[i + 3]) + s_bias[c0 + i + 3];
-                    if (P.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-                    __stcs(reinterpret_cast<float4*>(yr + c0 + i), o);      // written once, not re-read here
-                }
+        if (g == 0) issue_rows(next);                                        // in flight during the MMAs and both epilogues
+        if (N1 > 0) {
+            if (prev_tile >= 0) epilogue(prev_tile, N0, N1);                 // half 1 of the previous tile, under this tile's half 0
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncthreads();                                                 // every thread has drained half 1
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                mma_half(N0, N1, bar_d1);
             }
         }
-        // the next tile overwrites the A columns and the accumulator: every thread must be done reading
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
+        mbar_wait(bar_d0, ph_d0);
+        ph_d0 ^= 1;
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        epilogue(tile, 0, N0);                                               // half 0, under this tile's half 1
+        prev_tile = tile;
+        cur = nxt;
     }
+    if (N1 > 0) {
+        mbar_wait(bar_d1, ph_d1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        epilogue(prev_tile, N0, N1);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
 }
 

@@ -389,7 +389,7 @@ int unast_create(int device, unast_ctx** out) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<float, FE32_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<float, FE32_WARPS>::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, FE64_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, FE64_WARPS>::bytes);
     c->items.w = c->it_w; c->items.k0 = c->it_k0; c->items.mel = c->it_mel;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(prenet_fc1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pre_packed_bytes(PRE_MAXN) + 64);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(prenet_fc1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pre_smem_bytes(PRE_MAXN));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
@@ -893,12 +893,12 @@ int unast_mel_augment(unast_ctx* c, const float* x, int B, int T, int D, const i
 
 // ---- masking ops + first prenet layer on the tensor cores (8(f) rank 2) ----
 size_t unast_prenet_packed_bytes(int n_out) {
-    if (n_out < 16 || n_out > PRE_MAXN || (n_out & 15)) return 0;
+    if (n_out < 32 || n_out > PRE_MAXN || (n_out & 31)) return 0;
     return (size_t)pre_packed_bytes(n_out);
 }
 
 int unast_prenet_pack(unast_ctx* c, const float* weight, const float* bias, int n_out, void* packed_out, void* stream) {
-    if (!c || !weight || !packed_out || unast_prenet_packed_bytes(n_out) == 0) return fail(UNAST_E_ARG, "unast_prenet_pack: bad argument (n_out must be a multiple of 16, 16..256)");
+    if (!c || !weight || !packed_out || unast_prenet_packed_bytes(n_out) == 0) return fail(UNAST_E_ARG, "unast_prenet_pack: bad argument (n_out must be a multiple of 32, 32..256)");
     if ((uintptr_t)packed_out & 15) return fail(UNAST_E_ARG, "unast_prenet_pack: packed_out must be 16-byte aligned");
     DeviceGuard guard(c->device);
     if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
@@ -926,7 +926,7 @@ int unast_mel_prenet_fc1(unast_ctx* c, const float* x, int B, int T, const int32
     P.replace_with_zero = replace_with_zero; P.relu = relu; P.packed = (const unsigned char*)packed;
     const long long tiles = ((long long)B * T + PRE_TILE_M - 1) / PRE_TILE_M;
     const int grid = (int)std::min<long long>(tiles, c->num_sms);
-    const size_t smem = ((size_t)pre_packed_bytes(n_out) + 15) / 16 * 16 + 32;
+    const size_t smem = (size_t)pre_smem_bytes(n_out);
     prenet_fc1_kernel<<<grid, PRE_THREADS, smem, st>>>(P);
     CU(cudaGetLastError());
     return UNAST_OK;

@@ -271,7 +271,7 @@ class SpectralEngine:
         n_out = int(weight.shape[0])
         nbytes = self.lib.unast_prenet_packed_bytes(n_out)
         if nbytes == 0:
-            raise ValueError("n_out must be a multiple of 16 in 16..256")
+            raise ValueError("n_out must be a multiple of 32 in 32..256")
         w = weight.detach().to(self.device).contiguous()
         b = bias.detach().to(self.device, torch.float32).contiguous() if bias is not None else None
         packed = torch.empty(nbytes, dtype=torch.uint8, device=self.device)

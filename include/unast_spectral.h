@@ -132,6 +132,15 @@ typedef struct unast_gl_link {
     int32_t my_mail;
 } unast_gl_link;
 
+/* Canonical summation blocks (optional; default 0 = off).  With frames = G >= 4 the overlap-add of every later
+ * unast_griffinlim / unast_griffinlim_fragments call of this context restarts its running sums at every multiple of G
+ * frames of an utterance, whatever the cut into runs, fragments and ranks: a sample is then always (sum over the frames
+ * of one block, in frame order) + (the same of the next block), so the result is BIT-IDENTICAL for every sharding whose
+ * linked seams sit on multiples of G (a one-GPU run of the whole waveform included).  Costs granularity (runs are whole
+ * blocks): ~15 % on one GPU.  Off, the cut is chosen for speed and results of different shardings agree to ~1 ulp per
+ * iteration at the seams (which Griffin-Lim then amplifies like any other rounding). */
+int unast_griffinlim_set_block(unast_ctx* ctx, int frames);
+
 /* layout_out[5] = byte offsets of the three rotating overlap-add buffers and of the mailbox array inside a workspace
  * for these fragment sizes, and the workspace size (== unast_griffinlim_workspace_bytes).  Host-only, deterministic. */
 int unast_griffinlim_layout(const int32_t* frames_host, int B, float momentum, size_t* layout_out);

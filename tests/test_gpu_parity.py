@@ -633,6 +633,38 @@ def test_sharded_griffin_lim_protocol_emulated_on_one_gpu():
     assert np.array_equal(wav.cpu().numpy()[s:e], full)
 
 
+def test_sharded_griffin_lim_canonical_blocks_are_bit_identical_for_every_cut():
+    """unast_griffinlim_set_block: with canonical summation blocks the overlap-add no longer depends on how the frames are cut
+    into runs, fragments and ranks -- 1 / 2 / 3 / 5 / 7 fragments give the same bits (classic and momentum), the ordinary
+    whole-utterance entry point too, and the result stays within rounding of the speed-optimised cut."""
+    torch = _torch()
+    from unast_b200 import longform as LF, synth, utils as U
+    w = np.concatenate([synth.speech_like(8.0, 140 + i) for i in range(3)])            # 24 s, 1,925 frames (not a multiple of 4)
+    (mel, mag), = U.spectrograms_from_waves([w], do_trim=False)
+    n_iter = 15
+    mag_d = torch.from_numpy(mag).cuda()
+    one = LF.griffinlim_fragments_emulated(mag_d, 1, n_iter, canonical=True).cpu().numpy()
+    for world in (2, 3, 5, 7):
+        y = LF.griffinlim_fragments_emulated(mag_d, world, n_iter, canonical=True).cpu().numpy()
+        assert np.array_equal(y, one), world
+    eng = U.get_engine()
+    eng.set_gl_block(LF.GL_BLOCK)
+    try:
+        whole, = U._gl_batch([mag], n_iter, 0.0, None, 1.2, False, False)            # ordinary entry point, canonical blocks
+        pair = U._gl_batch([mag[:700], mag], n_iter, 0.0, None, 1.2, False, False)   # another batch composition: other run cuts
+    finally:
+        eng.set_gl_block(0)
+    assert np.array_equal(whole, one) and np.array_equal(pair[1], one)
+    fast, = U._gl_batch([mag], n_iter, 0.0, None, 1.2, False, False)
+    assert snr_db(fast, one) >= 80.0
+    rs = np.random.RandomState(4)                                                      # momentum variant, seeded phases
+    a0_d = torch.from_numpy(np.exp(2j * np.pi * rs.rand(mag.shape[0], 1025)).astype(np.complex64)).cuda()
+    ref = LF.griffinlim_fragments_emulated(mag_d, 1, 8, momentum=0.99, angles0=a0_d, canonical=True).cpu().numpy()
+    for world in (2, 4):
+        y = LF.griffinlim_fragments_emulated(mag_d, world, 8, momentum=0.99, angles0=a0_d, canonical=True).cpu().numpy()
+        assert np.array_equal(y, ref), world
+
+
 def test_prepare_streams_files_like_np_save(tmp_path):
     """prepare_data.prepare(): reader thread -> pinned staging -> GPU -> writer threads; the .npy files must be byte-identical
     to what np.save writes for the arrays get_spectrograms returns (prepare_data.py:33-34), over several chunks."""

@@ -216,6 +216,9 @@ def test_long_form_chunks_cover_what_their_frames_see():
         for world in (1, 2, 3, 8):
             rs = LF.frame_ranges(T, world)
             assert rs[0][0] == 0 and rs[-1][1] == T and all(rs[i][1] == rs[i + 1][0] for i in range(world - 1))
+            ra = LF.frame_ranges(T, world, align=LF.GL_BLOCK)                     # canonical Griffin-Lim blocks: aligned inner edges
+            assert ra[0][0] == 0 and ra[-1][1] == T and all(ra[i][1] == ra[i + 1][0] for i in range(world - 1))
+            assert all(e % LF.GL_BLOCK == 0 or e == T for _, e in ra[:-1]) and all(abs(x[1] - y[1]) <= LF.GL_BLOCK // 2 for x, y in zip(ra, rs))
             for a, b in rs:
                 c0, c1, keep = LF.chunk_for_range(n, a, b)
                 if b <= a:

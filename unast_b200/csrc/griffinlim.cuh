@@ -53,6 +53,8 @@ struct GlParams {
     float* ola[3];               // rotating overlap-add buffers: iteration `it` reads [it % 3], writes [(it + 1) % 3], re-zeroes
                                  // the seams of [(it + 2) % 3]
     int n_iter;
+    int block;                   // > 0: canonical summation blocks -- the carry restarts at every multiple of `block` frames of an
+                                 // utterance, so the overlap-add result does not depend on how the frames are cut into runs / ranks
     int* done;                   // [n_runs] epoch + number of iterations warp w has completed (incl. the initial inverse)
     int epoch;                   // base value of this call's progress counters (counters are never reset)
     int* abort;                  // set when a wait timed out; every wait loop leaves when it is set

@@ -232,7 +232,10 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
             const int L = HOP * (Tb - 1);
             const long long pos0 = ubase + HOP * t + WIN_LPAD;             // local padded index of the frame's tap 0
             const bool last_of_utt = t == Tb - 1;
-            const bool last_of_run = f == f1 - 1;
+            const bool run_end = f == f1 - 1;
+            // the carry is flushed where the run ends -- and, with canonical blocks, at every block boundary inside it
+            // (the warp then shares that seam with itself: tail added here, head added by the next frame)
+            const bool last_of_run = run_end || (P.block > 0 && (t + 1) % P.block == 0);
 
             if (!have_carry) {
                 for (int i = lane; i < GL_CARRY; i += 32) cb[i] = 0.0f;
@@ -471,7 +474,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                         if (q < seam_end) { atomicAdd(ola_w + q, cb[i]); if (pdst) atomicAdd(peer_wl + q, cb[i]); }
                         else ola_w[q] = cb[i];
                     }
-                } else if (link_r >= 0) {
+                } else if (link_r >= 0 && run_end) {
                     // linked tail seam: both copies get this side's partial sums; this side re-zeroes its own copy
                     for (int i = lane; i < OVERLAP; i += 32) {
                         const float c = cb[i];

@@ -108,6 +108,7 @@ struct unast_ctx {
     float4* it_w = nullptr; int* it_k0 = nullptr; int2* it_mel = nullptr;
     int* d_err = nullptr;
     int* d_abort = nullptr;
+    int gl_block = 0;                       // canonical Griffin-Lim summation block in frames (0 = off), unast_griffinlim_set_block
     std::vector<float> mel_basis;
 };
 
@@ -580,6 +581,12 @@ size_t unast_griffinlim_workspace_bytes(const int32_t* frames_host, int B, float
     return p.bytes;
 }
 
+int unast_griffinlim_set_block(unast_ctx* c, int frames) {
+    if (!c || (frames != 0 && (frames < 4 || frames > 64))) return fail(UNAST_E_ARG, "unast_griffinlim_set_block: 0 (off) or 4..64 frames");
+    c->gl_block = frames;
+    return UNAST_OK;
+}
+
 int unast_griffinlim_layout(const int32_t* frames_host, int B, float momentum, size_t* out5) {
     GlPlan p;
     if (!frames_host || !out5 || B <= 0) return fail(UNAST_E_ARG, "unast_griffinlim_layout: bad argument");
@@ -620,6 +627,8 @@ int gl_run(unast_ctx* c, const float* mag_norm, const GlPlan& p, int B, const un
     memset(&P, 0, sizeof(P));
     P.S = S; P.frame_off = d.frame_off; P.pad_off = d.pad_off; P.t0 = d.t0; P.Tg = d.Tg; P.B = B;
     for (int k = 0; k < 3; ++k) P.ola[k] = d.ola[k];
+    const int blk = c->gl_block;
+    P.block = blk;
     P.n_iter = n_iter; P.done = (int*)(ws + p.o_sync); P.epoch = epoch; P.abort = c->d_abort; P.err = c->d_err;
     P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
     P.angles0 = (const float2*)angles0;
@@ -637,6 +646,8 @@ int gl_run(unast_ctx* c, const float* mag_norm, const GlPlan& p, int B, const un
         if (L.fragment < 0 || L.fragment >= B || (L.side != 0 && L.side != 1) || L.my_mail < 0 || L.my_mail >= GL_MAX_LINKS || !L.peer_mail)
             return fail(UNAST_E_ARG, "unast_griffinlim: bad link");
         const int b = L.fragment, n = p.frame_off[b + 1] - p.frame_off[b];
+        if (blk > 0 && (L.side == 0 ? p.t0[b] : p.t0[b] + n) % blk)
+            return fail(UNAST_E_ARG, "unast_griffinlim: with canonical blocks a linked seam must sit on a multiple of the block");
         long long seam0;                                               // local index of the seam's first sample
         if (L.side == 0) {
             if (p.t0[b] == 0 || link_at_start[b] >= 0) return fail(UNAST_E_ARG, "unast_griffinlim: left link on a fragment that starts its utterance");
@@ -680,20 +691,46 @@ int gl_run(unast_ctx* c, const float* mag_norm, const GlPlan& p, int B, const un
         wsum += wseg[s];
     }
     while (wsum > Wmax) { int big = 0; for (int s = 1; s < nseg; ++s) if (wseg[s] > wseg[big]) big = s; --wseg[big]; --wsum; }
+    // canonical mode: run boundaries sit on block boundaries of their utterance (or on a fragment's edge)
+    auto frag_of = [&](int f) {                                          // fragment holding frame f < total
+        int lo = 0, hi = B;
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (p.frame_off[mid] <= f) lo = mid; else hi = mid; }
+        return lo;
+    };
+    auto boundary_after = [&](int f) {                                   // smallest boundary > f
+        const int bb = frag_of(f), t = f - p.frame_off[bb] + p.t0[bb];
+        return std::min(f + ((t / blk + 1) * blk - t), p.frame_off[bb + 1]);
+    };
+    auto snap = [&](int f, int prev, int end) {                          // boundary nearest to f, above prev, at most end
+        if (f >= end) return end;
+        const int bb = frag_of(f), t = f - p.frame_off[bb] + p.t0[bb];
+        int g = f;
+        if (t % blk) {
+            const int lo = std::max(f - t % blk, p.frame_off[bb]), hi = boundary_after(f);
+            g = (f - lo <= hi - f) ? lo : hi;
+        }
+        while (g <= prev) g = boundary_after(g);
+        return std::min(g, end);
+    };
     std::vector<int4> runs;
     runs.reserve(wsum);
     int b = 0;
     for (int s = 0; s < nseg; ++s) {
         const long long c0 = cost_of_frame_index(cut[s]), c1 = cost_of_frame_index(cut[s + 1]);
         int prev = cut[s];
-        for (int i = 0; i < wseg[s]; ++i) {
+        for (int i = 0; i < wseg[s] && prev < cut[s + 1]; ++i) {
             int f1 = i + 1 == wseg[s] ? cut[s + 1] : frame_at(p, B, c0 + (c1 - c0) * (i + 1) / wseg[s]);
-            f1 = std::max(f1, prev + 1);
-            f1 = std::min(f1, cut[s + 1] - (wseg[s] - 1 - i));
+            if (blk > 0) {
+                f1 = snap(f1, prev, cut[s + 1]);
+                if (cut[s + 1] - f1 < 2 * blk) f1 = cut[s + 1];              // no sliver at the end of a segment
+            } else {
+                f1 = std::max(f1, prev + 1);
+                f1 = std::min(f1, cut[s + 1] - (wseg[s] - 1 - i));
+            }
             while (b + 1 < B && p.frame_off[b + 1] <= prev) ++b;
             int ll = -1, lr = -1;
-            if (i == 0 && prev == p.frame_off[b]) ll = link_at_start[b];
-            if (i + 1 == wseg[s]) {                                       // the fragment this run ends in
+            if (prev == cut[s] && prev == p.frame_off[b]) ll = link_at_start[b];
+            if (f1 == cut[s + 1]) {                                       // the fragment this run ends in
                 int be = b;
                 while (be + 1 < B && p.frame_off[be + 1] < f1) ++be;
                 if (f1 == p.frame_off[be + 1]) lr = link_at_end[be];

@@ -264,6 +264,12 @@ class SpectralEngine:
         self.launches += 2 if (spans is not None and not replace_with_zero) else 1
         return out
 
+    def set_gl_block(self, frames):
+        """Canonical Griffin-Lim summation blocks (include/unast_spectral.h: unast_griffinlim_set_block): 0 = off (default),
+        G >= 4 makes every later Griffin-Lim call of this engine independent of the cut into runs / fragments / ranks."""
+        L.check(self.lib.unast_griffinlim_set_block(self.h, int(frames)))
+        self.gl_block = int(frames)
+
     def prenet_pack(self, weight, bias=None):
         """nn.Linear(80 -> n_out) parameters -> the shared-memory image unast_mel_prenet_fc1 uses (repack after an update)."""
         if weight.dtype != torch.float32 or weight.dim() != 2 or weight.shape[1] != NMELS:

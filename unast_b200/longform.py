@@ -31,9 +31,12 @@ HALO = 4                     # frames: 4 * 275 = 1100 >= 552 samples on either s
 NMELS = ap.n_mels
 
 
-def frame_ranges(n_frames, world):
-    """Contiguous, near-equal frame ranges [(a, b)] for ranks 0..world-1 (some may be empty for tiny inputs)."""
+def frame_ranges(n_frames, world, align=1):
+    """Contiguous, near-equal frame ranges [(a, b)] for ranks 0..world-1 (some may be empty for tiny inputs); inner
+    edges are multiples of `align`."""
     edges = [(n_frames * r) // world for r in range(world + 1)]
+    if align > 1:
+        edges = [0] + [min(n_frames, (e + align // 2) // align * align) for e in edges[1:-1]] + [n_frames]
     return [(edges[r], edges[r + 1]) for r in range(world)]
 
 
@@ -87,6 +90,7 @@ def spectrograms_long(wave, rank=0, world=1, precision=None, do_trim=True):
 
 SEAM0 = (ap.n_fft - ap.win_length) // 2           # 473: padded position of a frame's first tap relative to 275 t
 GL_MIN_FRAGMENT = 9
+GL_BLOCK = 4                 # canonical summation block: a sample is covered by at most 5 consecutive frames = 2 blocks
 
 
 def _links_for(eng, my_frames, my_base, left=None, right=None, momentum=0.0):
@@ -109,13 +113,17 @@ def _links_for(eng, my_frames, my_base, left=None, right=None, momentum=0.0):
 class ShardedGriffinLim:
     """Griffin-Lim on ONE long spectrogram of T frames, frames sharded by contiguous ranges over the ranks of the default
     process group (one process per GPU).  Construct once per (T, momentum) on every rank (collective: exchanges the CUDA
-    IPC handles of the workspaces), then `run()` any number of times."""
+    IPC handles of the workspaces), then `run()` any number of times.
 
-    def __init__(self, T, rank, world, momentum=0.0):
+    canonical=True: the overlap-add sums are grouped in blocks of GL_BLOCK frames of the waveform whatever the sharding, so
+    the result is bit-identical for every world size (one GPU included), at ~15 % of the single-GPU speed."""
+
+    def __init__(self, T, rank, world, momentum=0.0, canonical=False):
         import torch.distributed as dist
         self.eng = get_engine()
         self.T, self.rank, self.world, self.momentum = int(T), int(rank), int(world), float(momentum)
-        self.ranges = frame_ranges(self.T, self.world)
+        self.block = GL_BLOCK if canonical else 0
+        self.ranges = frame_ranges(self.T, self.world, align=max(1, self.block))
         self.a, self.b = self.ranges[self.rank]
         sizes = [e - s for s, e in self.ranges]
         if self.world > 1 and min(sizes) < GL_MIN_FRAGMENT:
@@ -141,9 +149,13 @@ class ShardedGriffinLim:
     def run(self, mag_rows, n_iter, angles0_rows=None, power=ap.power, raw_out=None):
         """mag_rows: this rank's rows [a, b) of the normalised magnitude spectrogram (device float32 [b - a, 1025]).
         Returns this rank's owned samples of istft(S * angles) after n_iter iterations (device float32), asynchronous."""
-        raw, _ = self.eng.griffinlim_fragments(mag_rows, [self.b - self.a], [self.a], [self.T], self.links, epoch=self.epoch,
-                                               n_iter=n_iter, momentum=self.momentum, angles0=angles0_rows, power=power,
-                                               workspace=self.ws, raw_out=raw_out)
+        self.eng.set_gl_block(self.block)
+        try:
+            raw, _ = self.eng.griffinlim_fragments(mag_rows, [self.b - self.a], [self.a], [self.T], self.links, epoch=self.epoch,
+                                                   n_iter=n_iter, momentum=self.momentum, angles0=angles0_rows, power=power,
+                                                   workspace=self.ws, raw_out=raw_out)
+        finally:
+            self.eng.set_gl_block(0)
         self.epoch += int(n_iter) + 2
         return raw
 
@@ -195,13 +207,14 @@ class ShardedGriffinLim:
 _EMU_EPOCH = [1]
 
 
-def griffinlim_fragments_emulated(mag, world, n_iter, momentum=0.0, angles0=None, power=ap.power):
+def griffinlim_fragments_emulated(mag, world, n_iter, momentum=0.0, angles0=None, power=ap.power, canonical=False):
     """The sharded run's protocol on ONE GPU: the T frames of `mag` (device float32 [T, 1025]) cut into `world` fragments
     that are processed by one launch, every cut a linked seam whose two copies live in the same workspace.  Returns the
-    raw (normalised, not de-emphasised) waveform [275 (T - 1)] as a device tensor."""
+    raw (normalised, not de-emphasised) waveform [275 (T - 1)] as a device tensor.  canonical=True: summation blocks of
+    GL_BLOCK frames -- the result is then bit-identical for every `world`."""
     eng = get_engine()
     T = int(mag.shape[0])
-    ranges = frame_ranges(T, world)
+    ranges = frame_ranges(T, world, align=GL_BLOCK if canonical else 1)
     frames = [e - s for s, e in ranges]
     t0 = [s for s, _ in ranges]
     if world > 8 or (world > 1 and min(frames) < GL_MIN_FRAGMENT):
@@ -216,8 +229,12 @@ def griffinlim_fragments_emulated(mag, world, n_iter, momentum=0.0, angles0=None
                       "peer_ola": [base + lay[k] + 4 * (int(pad[i + 1]) + SEAM0) for k in range(3)]})
         links.append({"fragment": i + 1, "side": 0, "my_mail": slot_r, "peer_mail": base + lay[3] + 4 * slot_l,
                       "peer_ola": [base + lay[k] + 4 * (int(pad[i]) + HOP * frames[i] + SEAM0) for k in range(3)]})
-    raw, _ = eng.griffinlim_fragments(mag, frames, t0, [T] * world, links, epoch=_EMU_EPOCH[0], n_iter=n_iter, momentum=momentum,
-                                      angles0=angles0, power=power, workspace=base)
+    eng.set_gl_block(GL_BLOCK if canonical else 0)
+    try:
+        raw, _ = eng.griffinlim_fragments(mag, frames, t0, [T] * world, links, epoch=_EMU_EPOCH[0], n_iter=n_iter, momentum=momentum,
+                                          angles0=angles0, power=power, workspace=base)
+    finally:
+        eng.set_gl_block(0)
     _EMU_EPOCH[0] += int(n_iter) + 2
     return raw
 

@@ -104,7 +104,7 @@ __device__ __forceinline__ bool gl_wait(const int* p, int target, int* abort_fla
     return ok != 0;
 }
 
-template <bool MOMENTUM>
+template <bool MOMENTUM, bool CANON>
 __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlParams P) {
     constexpr int NT = GL_WARPS * 32;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
             const bool run_end = f == f1 - 1;
             // the carry is flushed where the run ends -- and, with canonical blocks, at every block boundary inside it
             // (the warp then shares that seam with itself: tail added here, head added by the next frame)
-            const bool last_of_run = run_end || (P.block > 0 && (t + 1) % P.block == 0);
+            const bool last_of_run = run_end || (CANON && (t + 1) % P.block == 0);
 
             if (!have_carry) {
                 for (int i = lane; i < GL_CARRY; i += 32) cb[i] = 0.0f;

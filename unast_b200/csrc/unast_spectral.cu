@@ -391,8 +391,10 @@ int unast_create(int device, unast_ctx** out) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, FE64_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, FE64_WARPS>::bytes);
     c->items.w = c->it_w; c->items.k0 = c->it_k0; c->items.mel = c->it_mel;
     if (e == cudaSuccess) e = cudaFuncSetAttribute(prenet_fc1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pre_smem_bytes(PRE_MAXN));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gl_persist_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, glp_smem_bytes);
     if (e != cudaSuccess) { unast_destroy(c); return fail(UNAST_E_CUDA, std::string("unast_create: ") + cudaGetErrorString(e)); }
     *out = c;
     return UNAST_OK;
@@ -746,7 +748,8 @@ int gl_run(unast_ctx* c, const float* mag_norm, const GlPlan& p, int B, const un
     // one cooperative launch: every CTA must be resident, warps wait for one another
     const int grid = (P.n_runs + GL_WARPS - 1) / GL_WARPS;
     void* args[] = {(void*)&P};
-    const void* fn = momentum != 0.f ? (const void*)gl_persist_kernel<true> : (const void*)gl_persist_kernel<false>;
+    const void* fn = blk > 0 ? (momentum != 0.f ? (const void*)gl_persist_kernel<true, true> : (const void*)gl_persist_kernel<false, true>)
+                             : (momentum != 0.f ? (const void*)gl_persist_kernel<true, false> : (const void*)gl_persist_kernel<false, false>);
     CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(GL_WARPS * 32), args, (size_t)glp_smem_bytes, st));
     return UNAST_OK;
 }

@@ -76,7 +76,10 @@ struct GlParams {
     const double* w2;            // [1102] hann^2 in float64 (exact edge envelope for very short utterances)
 };
 
-constexpr int GL_WARPS = 16;
+#ifndef GL_WARPS_N
+#define GL_WARPS_N 16
+#endif
+constexpr int GL_WARPS = GL_WARPS_N;
 constexpr int GL_XS_BYTES = xs_bytes<float>();                   // 4608: transposition buffer
 constexpr int GL_CARRY = 828;                                     // 827 carried samples + one zero
 

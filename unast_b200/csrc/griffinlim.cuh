@@ -1,4 +1,4 @@
-// K3 building blocks: parameter block and constants of the Griffin-Lim iteration kernel gl_pk_kernel (griffinlim_pk.cuh; replaces reference src/utils.py:309-328 and librosa.griffinlim as
+// K3 building blocks: parameter block and constants of the Griffin-Lim iteration kernel gl_persist_kernel (griffinlim_pk.cuh; replaces reference src/utils.py:309-328 and librosa.griffinlim as
 // called at src/gl_vocoder.py:26).
 //
 // State carried between iterations is the *time-domain* overlap-add buffer (raw window-weighted sums,

@@ -114,6 +114,32 @@ def test_deemphasis_inverts_preemphasis():
     assert np.abs(so.deemphasis(pre) - y).max() < 1e-9
 
 
+def test_forward_chain_against_torchaudio_transforms():
+    """Independent witness for the forward chain after the trim: torchaudio's own pre-emphasis, Spectrogram (its framing,
+    reflect padding, zero-padded Hann), Slaney MelScale and amplitude_to_DB, in float64, against the oracle's float32 path --
+    no code shared with oracle/ or with tests/golden/make_golden.py's stand-ins beyond torch.stft."""
+    torch = pytest.importorskip("torch")
+    ta = pytest.importorskip("torchaudio")
+    y = _speechy(22050, 3).astype(np.float32)
+    mel, mag = so.spectrograms_from_wave(y, do_trim=False)
+    yt = torch.from_numpy(y.astype(np.float64))
+    pre = torch.cat([yt[:1], ta.functional.preemphasis(yt, 0.97)[1:]])          # utils.py:251 keeps y[0]; torchaudio's first sample is y[0] too
+    spec = ta.transforms.Spectrogram(n_fft=2048, win_length=1102, hop_length=275, power=1.0, center=True, pad_mode="reflect",
+                                     window_fn=lambda n: torch.hann_window(n, periodic=True, dtype=torch.float64))(pre)
+    fb = ta.functional.melscale_fbanks(1025, 0.0, 11025.0, 80, 22050, norm="slaney", mel_scale="slaney").to(torch.float64)
+    mel_t = fb.T @ spec
+    db = lambda x: ta.functional.amplitude_to_DB(x, 20.0, 1e-5, 0.0)             # 20 log10(max(1e-5, x))
+    nrm = lambda d: torch.clamp((d - 20.0 + 100.0) / 100.0, 1e-8, 1.0)
+    # float64 against the reference's float32 samples / complex64 spectra: the north-star gate (1e-4) on every bin -- the
+    # largest differences sit in bins ~100 dB below the frame peak -- and rounding level on the typical one
+    dg, dm = np.abs(nrm(db(spec)).numpy().T - mag), np.abs(nrm(db(mel_t)).numpy().T - mel)
+    assert dg.max() <= 1e-4 and dm.max() <= 1e-4 and np.median(dg) <= 1e-6 and np.median(dm) <= 1e-6
+    # de-emphasis (utils.py:301): torchaudio's IIR against scipy.signal.lfilter as the oracle calls it
+    w = torch.from_numpy(np.random.RandomState(2).randn(4000))
+    iir = ta.functional.lfilter(w, torch.tensor([1.0, -0.97], dtype=torch.float64), torch.tensor([1.0, 0.0], dtype=torch.float64), clamp=False)
+    assert np.abs(iir.numpy() - so.deemphasis(w.numpy())).max() <= 1e-9     # (torchaudio's own deemphasis() clamps to [-1, 1])
+
+
 # ---- next row: specaugment / noise_fn (src/utils.py:40-75), pinned on the reference's own output ----
 def _seed(seed):
     import random
@@ -203,6 +229,32 @@ def test_istft_against_torch_and_scipy():
                                input_onesided=True, boundary=True)
     n = min(ys.size, mine.size)
     assert np.abs(mine[2048:n - 2048] - ys[2048:n - 2048]).max() <= 2e-6
+
+
+def test_griffin_lim_loops_against_torchaudio():
+    """Independent witness for the two Griffin-Lim loops: torchaudio.functional.griffinlim (its own stft / istft / momentum
+    update, float64) started from the same phases -- momentum 0.99 == librosa.griffinlim as gl_vocoder.py:26 calls it,
+    momentum 0 == the classic loop of utils.py:309-320 (the phase normalisations differ only below 1e-8)."""
+    torch = pytest.importorskip("torch")
+    taf = pytest.importorskip("torchaudio.functional")
+    y = _speechy(275 * 80, 9)
+    S = np.abs(so.stft(y)).astype(np.float32)                                    # [1025, 81]
+    win = torch.zeros(2048, dtype=torch.float64)
+    win[473:473 + 1102] = torch.from_numpy(0.5 - 0.5 * np.cos(2 * np.pi * np.arange(1102) / 1102))
+    St = torch.from_numpy(S.astype(np.float64))
+
+    def snr(a, b):
+        a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+        return 10 * np.log10((a ** 2).sum() / max(((a - b) ** 2).sum(), 1e-300))
+
+    for iters in (1, 4, 12):
+        # rand_init=False starts torchaudio from unit phases: the zero-phase start of the reference / init=None of librosa
+        ref_m = taf.griffinlim(St, win, 2048, 275, 2048, 1.0, iters, 0.99, 275 * 80, False).numpy()
+        mine_m = so.librosa_griffinlim(S, iters=iters, momentum=0.99, angles0=np.ones(S.shape, np.complex64))
+        assert mine_m.shape == ref_m.shape and snr(ref_m, mine_m) >= 85.0, (iters, snr(ref_m, mine_m))
+        ref_c = taf.griffinlim(St, win, 2048, 275, 2048, 1.0, iters, 0.0, 275 * 80, False).numpy()
+        mine_c = so.griffin_lim(S.astype(np.complex64), iters=iters)
+        assert mine_c.shape == ref_c.shape and snr(ref_c, mine_c) >= 85.0, (iters, snr(ref_c, mine_c))
 
 
 def test_window_sumsquare_brute_force():

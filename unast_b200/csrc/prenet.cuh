@@ -114,7 +114,7 @@ static_assert(pre_smem_bytes(PRE_MAXN) <= 227 * 1024, "shared memory layout");
 //   * output: the two warps of a quadrant drain 16 rows each with tcgen05.ld.16x256b -- a row's 8 columns arrive spread over
 //     four lanes, so every store instruction writes eight full 32-byte sectors, with no shared-memory transposition.
 __global__ void __launch_bounds__(PRE_THREADS, 1) prenet_fc1_kernel(const PrenetParams P) {
-    extern __shared__ __align__(128) unsigned char smem[];
+    extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int q = warp & 3, g = warp >> 2;                                   // lane quadrant, half of the quadrant's work
     const int N = P.N;

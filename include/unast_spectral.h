@@ -178,6 +178,17 @@ size_t unast_mel_augment_workspace_bytes(int B);
 int unast_mel_augment(unast_ctx* ctx, const float* x, int B, int T, int D, const int32_t* spans, const float* keep,
                       int replace_with_zero, float* out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* unast_mel_augment for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  Same arguments and results as
+ * unast_mel_augment without the workspace: the partial sums of the mean live in a file-scope __device__ array of the library
+ * (UNAST_AUG_STATIC_MAX_B x 32 doubles = 256 KB, held by every GPU that loads the library until the process exits), and the
+ * call performs no cudaMalloc / cudaFree / allocating library call.  B > UNAST_AUG_STATIC_MAX_B returns UNAST_E_ARG.
+ * Every call on a device shares that array (it keeps the last call's contents; each call overwrites what it reads, nothing
+ * needs clearing): calls that overlap on the GPU -- different streams, or two contexts of one device -- race; serialise them. */
+#define UNAST_AUG_STATIC_MAX_B 1024
+int unast_mel_augment_static(unast_ctx* ctx, const float* x, int B, int T, int D, const int32_t* spans, const float* keep,
+                             int replace_with_zero, float* out, void* stream);
+
 /* The masking ops above fused with the first layer of SpeechPrenet (module.py:93-95: fc1 = Linear(num_mels -> s_pre_hid),
  * ReLU), on the tensor cores (tcgen05.mma, A operand in tensor memory, float32 fidelity by operand splitting):
  *     y[b][t][:] = relu(W ((t in a span ? fill_b : x[b][t][:]) * keep[b][t]) + bias)          x: [B][T][80], y: [B][T][n_out]

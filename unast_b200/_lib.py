@@ -45,6 +45,7 @@ SYMBOLS = [
     ("unast_mel_augment_workspace_bytes", _sz, [_i]),
     ("unast_mel_augment", _i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
     ("unast_griffinlim_set_block", _i, [_vp, _i]),
+    ("unast_mel_augment_static", _i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp]),
     ("unast_prenet_packed_bytes", _sz, [_i]),
     ("unast_prenet_pack", _i, [_vp, _vp, _vp, _i, _vp, _vp]),
     ("unast_mel_prenet_fc1", _i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp, _i, _i, _vp, _vp, _sz, _vp]),

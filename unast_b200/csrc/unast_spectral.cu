@@ -109,8 +109,15 @@ struct unast_ctx {
     int* d_err = nullptr;
     int* d_abort = nullptr;
     int gl_block = 0;                       // canonical Griffin-Lim summation block in frames (0 = off), unast_griffinlim_set_block
+    double* aug_static = nullptr;           // device address of g_aug_static_parts on this context's device (unast_create)
+    cudaError_t aug_static_err = cudaSuccess;
     std::vector<float> mel_basis;
 };
+
+// ---- scratch of unast_mel_augment_static: file scope, UNAST_AUG_STATIC_MAX_B x AUG_PARTS partial sums = 256 KB, held by every GPU
+// that loads the library until the process exits.  In HOST code this name is a stand-in, not a device address: the address
+// each device gives it is taken once per context with cudaGetSymbolAddress (unast_create, that device current).
+static __device__ __align__(256) double g_aug_static_parts[UNAST_AUG_STATIC_MAX_B * unast::AUG_PARTS];
 
 // ---- diagnostics kernels ----------------------------------------------------------------------
 namespace unast {
@@ -387,6 +394,12 @@ int unast_create(int device, unast_ctx** out) {
     if (e == cudaSuccess) e = cudaMemset(c->d_err, 0, sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_abort, sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->d_abort, 0, sizeof(int));
+    if (e == cudaSuccess) {                                             // a failure here only disables unast_mel_augment_static
+        void* sym = nullptr;
+        c->aug_static_err = cudaGetSymbolAddress(&sym, g_aug_static_parts);
+        c->aug_static = c->aug_static_err == cudaSuccess ? (double*)sym : nullptr;
+        if (c->aug_static_err != cudaSuccess) (void)cudaGetLastError();
+    }
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<float, FE32_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<float, FE32_WARPS>::bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_au_kernel<double, FE64_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeAuLayout<double, FE64_WARPS>::bytes);
     c->items.w = c->it_w; c->items.k0 = c->it_k0; c->items.mel = c->it_mel;
@@ -921,6 +934,36 @@ int unast_mel_augment(unast_ctx* c, const float* x, int B, int T, int D, const i
     double* parts = (double*)workspace;
     if (need_mean) aug_sum_kernel<<<dim3(AUG_PARTS, B), AUG_THREADS, 0, st>>>(x, slab, parts);
     // enough CTAs per utterance to fill the machine a few times over, at least 8 float4 per thread
+    long long per = (slab / 4 + AUG_THREADS * 8 - 1) / (AUG_THREADS * 8);
+    const long long want = ((long long)c->num_sms * 8 + B - 1) / B;
+    if (per > want) per = want;
+    if (per < 1) per = 1;
+    aug_apply_kernel<<<dim3((unsigned)per, B), AUG_THREADS, 0, st>>>(x, out, T, D, spans, keep, need_mean ? parts : nullptr,
+                                                                     replace_with_zero);
+    CU(cudaGetLastError());
+    return UNAST_OK;
+}
+
+// The same two launches as unast_mel_augment with the partial sums of the mean in g_aug_static_parts: no workspace argument,
+// no cudaMalloc / cudaFree / allocating library call on this path.  aug_sum_kernel overwrites every partial sum of utterances
+// 0..B-1 with a plain store before aug_apply_kernel reads it, so nothing has to start at zero; calls that overlap on the GPU
+// (two streams, two contexts of one device) share the array and race.
+int unast_mel_augment_static(unast_ctx* c, const float* x, int B, int T, int D, const int32_t* spans, const float* keep,
+                             int replace_with_zero, float* out, void* stream) {
+    if (!c || !x || !out || B <= 0 || T <= 0 || D <= 0) return fail(UNAST_E_ARG, "unast_mel_augment_static: bad argument");
+    if (B > UNAST_AUG_STATIC_MAX_B)
+        return fail(UNAST_E_ARG, "unast_mel_augment_static: B exceeds UNAST_AUG_STATIC_MAX_B (1024 utterances); use unast_mel_augment with a workspace");
+    const bool need_mean = spans && !replace_with_zero;
+    if (need_mean && x == out) return fail(UNAST_E_ARG, "unast_mel_augment_static: in-place needs replace_with_zero or no spans");
+    if (spans && ((uintptr_t)spans & 15)) return fail(UNAST_E_ARG, "unast_mel_augment_static: spans must be 16-byte aligned");
+    if (!c->aug_static)
+        return fail(UNAST_E_CUDA, std::string("unast_mel_augment_static: cudaGetSymbolAddress failed at set-up: ") + cudaGetErrorString(c->aug_static_err));
+    DeviceGuard guard(c->device);
+    if (!guard.ok()) return fail(UNAST_E_CUDA, "cannot select the context's device");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long slab = (long long)T * D;
+    double* parts = c->aug_static;                                       // the device address, never the symbol's name
+    if (need_mean) aug_sum_kernel<<<dim3(AUG_PARTS, B), AUG_THREADS, 0, st>>>(x, slab, parts);
     long long per = (slab / 4 + AUG_THREADS * 8 - 1) / (AUG_THREADS * 8);
     const long long want = ((long long)c->num_sms * 8 + B - 1) / B;
     if (per > want) per = want;

@@ -264,6 +264,16 @@ class SpectralEngine:
         self.launches += 2 if (spans is not None and not replace_with_zero) else 1
         return out
 
+    def mel_augment_static(self, x, out, spans=None, keep=None, replace_with_zero=False):
+        """mel_augment for callers that must not allocate (include/unast_spectral.h: unast_mel_augment_static): `out` is
+        required, the scratch is the library's file-scope device array (B <= 1024), no torch or CUDA allocation happens here.
+        Calls that overlap on the GPU share that array and race."""
+        B, T, D = (int(v) for v in x.shape)
+        L.check(self.lib.unast_mel_augment_static(self.h, _ptr(x), B, T, D, _ptr(spans), _ptr(keep), 1 if replace_with_zero else 0,
+                                                  _ptr(out), self._stream()))
+        self.launches += 2 if (spans is not None and not replace_with_zero) else 1
+        return out
+
     def set_gl_block(self, frames):
         """Canonical Griffin-Lim summation blocks (include/unast_spectral.h: unast_griffinlim_set_block): 0 = off (default),
         G >= 4 makes every later Griffin-Lim call of this engine independent of the cut into runs / fragments / ranks."""

@@ -57,38 +57,68 @@ __host__ __device__ constexpr int brev5(int i) {
     return ((i & 1) << 4) | ((i & 2) << 2) | (i & 4) | ((i & 8) >> 2) | ((i & 16) >> 4);
 }
 
+// One radix-2 decimation-in-time butterfly with the twiddle folded into the additions:
+//   x = a + W b,  y = a - W b,   W = exp(-2 pi i J / 32), J in 0..15
+// General W = c - i s: x in four fused multiply-adds, y = 2 a - x in two more (6 instructions against 8 for multiply-then-add);
+// W = (+-1 - i) / sqrt 2: two additions and four fused multiply-adds; W = 1, -i: four additions.
+template <int J, class C>
+__device__ __forceinline__ void bfly_w32(C a, C b, C& x, C& y) {
+    using T = decltype(a.x);
+    if constexpr (J == 0) {
+        x = cadd(a, b);
+        y = csub(a, b);
+    } else if constexpr (J == 8) {                       // W b = (b.y, -b.x)
+        x = mk(a.x + b.y, a.y - b.x);
+        y = mk(a.x - b.y, a.y + b.x);
+    } else if constexpr (J == 4) {                       // W b = r (b.x + b.y, b.y - b.x)
+        constexpr T r = (T)kCos32[4];
+        const T sm = b.x + b.y, df = b.y - b.x;
+        x = mk(fma_t(r, sm, a.x), fma_t(r, df, a.y));
+        y = mk(fma_t(-r, sm, a.x), fma_t(-r, df, a.y));
+    } else if constexpr (J == 12) {                      // W b = r (b.y - b.x, -(b.x + b.y))
+        constexpr T r = (T)kCos32[4];
+        const T sm = b.x + b.y, df = b.y - b.x;
+        x = mk(fma_t(r, df, a.x), fma_t(-r, sm, a.y));
+        y = mk(fma_t(-r, df, a.x), fma_t(r, sm, a.y));
+    } else {                                             // W b = (c b.x + s b.y, c b.y - s b.x)
+        constexpr T c = (T)cos32(J), sn = (T)sin32(J);
+        x = mk(fma_t(c, b.x, fma_t(sn, b.y, a.x)), fma_t(c, b.y, fma_t(-sn, b.x, a.y)));
+        y = mk(fma_t((T)2, a.x, -x.x), fma_t((T)2, a.y, -x.y));
+    }
+}
+
 template <int SPAN, class C>
-__device__ __forceinline__ void dif_stage(C (&v)[32]) {
+__device__ __forceinline__ void dit_stage(C (&v)[32]) {
     static_for<0, 16>([&](auto ii) {
         constexpr int i = decltype(ii)::value;
         constexpr int base = (i / SPAN) * 2 * SPAN, j = i % SPAN;
-        C a = v[base + j], b = v[base + j + SPAN];
-        v[base + j] = cadd(a, b);
-        v[base + j + SPAN] = mul_w32<j*(16 / SPAN)>(csub(a, b));
+        bfly_w32<j*(16 / SPAN)>(v[base + j], v[base + j + SPAN], v[base + j], v[base + j + SPAN]);
     });
 }
 
-// In-register 32-point forward FFT (radix-2 DIF, natural order in and out).
-// NZ: only v[0..NZ) are non-zero on entry (16 <= NZ <= 32) -- prunes the first stage.
+// In-register 32-point forward FFT (radix-2 decimation in time on the bit-reversed registers -- a compile-time renaming --,
+// natural order in and out).
+// NZ: only v[0..NZ) are non-zero on entry (16 <= NZ <= 32): the first stage pairs (v[r], v[r + 16]); where v[r + 16] is zero
+// the butterfly is two copies.
 template <int NZ, class C>
 __device__ __forceinline__ void fft32(C (&v)[32]) {
     static_assert(NZ >= 16 && NZ <= 32, "pruning supports 16..32 live inputs");
-    static_for<0, 16>([&](auto jj) {
-        constexpr int j = decltype(jj)::value;
-        if constexpr (j + 16 < NZ) {
-            C a = v[j], b = v[j + 16];
-            v[j] = cadd(a, b);
-            v[j + 16] = mul_w32<j>(csub(a, b));
+    C t[32];
+    static_for<0, 16>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        constexpr int r = brev5(2 * i);                  // brev5(2 i + 1) == r + 16
+        if constexpr (r + 16 < NZ) {
+            t[2 * i] = cadd(v[r], v[r + 16]);
+            t[2 * i + 1] = csub(v[r], v[r + 16]);
         } else {
-            v[j + 16] = mul_w32<j>(v[j]);
+            t[2 * i] = v[r];
+            t[2 * i + 1] = v[r];
         }
     });
-    dif_stage<8>(v);
-    dif_stage<4>(v);
-    dif_stage<2>(v);
-    dif_stage<1>(v);
-    C t[32];
-    static_for<0, 32>([&](auto kk) { constexpr int k = decltype(kk)::value; t[k] = v[brev5(k)]; });
+    dit_stage<2>(t);
+    dit_stage<4>(t);
+    dit_stage<8>(t);
+    dit_stage<16>(t);
     static_for<0, 32>([&](auto kk) { constexpr int k = decltype(kk)::value; v[k] = t[k]; });
 }
 

@@ -539,6 +539,23 @@ def test_griffin_lim_benchmark_scale_batch():
         _check_gl(outs[i], ref, so.denormalise(mags[i]))
 
 
+def test_griffin_lim_from_the_oracles_target_magnitudes():
+    """The kernel alone: both sides start from the SAME target magnitudes S (the oracle's, passed through with power 0).  The
+    zero-phase start w * irfft(S) is computed in float64 (gl_init_f64_kernel): it is the tail of a large cancellation, and
+    the one step of the whole run whose float32 rounding decides the distance to the reference.  End to end (the CUDA path
+    de-normalising the magnitudes itself) the last-bit differences between numpy's SIMD float32 powf and correctly rounded
+    powers enter that same step: the tests above hold 40 dB there, this one holds 65 dB (measured 73-112 dB) and 130 dB at
+    zero iterations."""
+    from unast_b200 import utils as U
+    mags = _mags([(1.5, 1021), (2.7, 1005), (6.0, 1042)])
+    Ss = [np.ascontiguousarray(so.denormalise(m).T) for m in mags]
+    for iters, gate in ((0, 130.0), (100, 65.0)):
+        outs = U._gl_batch(Ss, iters, 0.0, None, 0.0, True, False)
+        for m, y in zip(mags, outs):
+            ref = so.spectrogram2wav(m, iters=iters, return_untrimmed=True)
+            assert y.shape == ref.shape and snr_db(ref, y) >= gate, (iters, snr_db(ref, y))
+
+
 def test_griffin_lim_long_waveform():
     """One 60 s spectrogram (4,811 frames: hundreds of warp runs and seams inside one utterance), 30 iterations."""
     from unast_b200 import synth, utils as U

@@ -107,6 +107,29 @@ def test_denormalise_formula():
     assert S.shape == (50, 3) and np.allclose(S, ref, rtol=2e-5)
 
 
+def test_zero_phase_start_amplifies_last_bit_differences_of_S():
+    """Why end-to-end Griffin-Lim parity is a statement about libm: numpy's SIMD float32 powf (what `denormalise` runs on
+    this image, like the reference's own statements would) is not correctly rounded, and the zero-phase start of
+    utils.griffin_lim (utils.py:311-313) turns last-bit differences of S into a visible difference of the waveform --
+    the reference differs from ITSELF by this much across numpy / libm versions."""
+    y = _speechy(22050, 11).astype(np.float32)
+    mag = so.spectrograms_from_wave(y, do_trim=False)[1]
+    S = so.denormalise(mag)                                                       # float32 statements of utils.py:289-298
+    c = np.clip(mag.T, 0, 1)
+    m = (c * np.float32(100) - np.float32(100) + np.float32(20)).astype(np.float32)
+    a = np.power(10.0, (m * np.float32(0.05)).astype(np.float64)).astype(np.float32)    # correctly rounded 10^x
+    S_cr = np.power(a.astype(np.float64), np.float64(np.float32(1.2))).astype(np.float32)   # correctly rounded a^1.2f
+    ulp = np.abs(S.view(np.int32).astype(np.int64) - S_cr.view(np.int32).astype(np.int64))
+    assert ulp.max() <= 4                                                          # the same numbers to the last few bits (measured: 3, 36 % of the bins)
+    x0, x1 = so.istft(S.astype(np.complex64)), so.istft(S_cr.astype(np.complex64))
+    d0 = 10 * np.log10((x0.astype(np.float64) ** 2).sum() / max(((x0.astype(np.float64) - x1) ** 2).sum(), 1e-300))
+    if (ulp > 0).mean() > 0.01:                                                   # (a libm with correctly rounded powf: nothing to see)
+        assert d0 < 135.0                                                          # float32 resolution would be ~ 150 dB
+        g0, g1 = so.griffin_lim(S.astype(np.complex64), iters=30), so.griffin_lim(S_cr.astype(np.complex64), iters=30)
+        d30 = 10 * np.log10((g0.astype(np.float64) ** 2).sum() / max(((g0.astype(np.float64) - g1) ** 2).sum(), 1e-300))
+        assert d30 < 110.0
+
+
 def test_deemphasis_inverts_preemphasis():
     rng = np.random.RandomState(1)
     y = rng.randn(5000)

@@ -10,7 +10,8 @@
 // fft32_ab maps A -> B.  The twiddle between the two passes multiplies pairs of layout B by a table laid out to
 // match, and the transposition writes element n1 of a row to column 2 (n1 % 16) + n1 / 16, so that the 128-bit
 // row reads of the second pass come back as layout-A pairs without a single register move.
-// Per 32-point transform: 175 packed + <= 128 scalar instructions instead of 456 scalar ones.
+// Per 32-point transform: 175 packed + <= 128 scalar instructions (A -> B, decimation in frequency), 148 packed + 92 scalar
+// (B -> A, decimation in time with the twiddles folded into fused multiply-adds), instead of 456 scalar ones.
 //
 // Replaces numpy.fft.rfft / irfft as called by librosa.stft / istft (reference src/utils.py:314, :328).
 #pragma once
@@ -190,50 +191,55 @@ __device__ __forceinline__ void warp_fft1024_pk(Pk& p, float* xs, const TAB& tw4
     fft32_ab<32>(p);
 }
 
-// (re, im) * (exp(-2 pi i J1 / 32), exp(-2 pi i J2 / 32)): a different twiddle in each half of the pair
-template <int J1, int J2>
-__device__ __forceinline__ void pk_mul_w32_2(float2& re, float2& im) {
-    if constexpr (J1 != 0 || J2 != 0) {
-        const float2 c = make_float2((float)cos32(J1), (float)cos32(J2)), s = make_float2((float)sin32(J1), (float)sin32(J2));
-        const float2 nr = __ffma2_rn(re, c, __fmul2_rn(im, s));
-        const float2 ni = __ffma2_rn(im, c, __fmul2_rn(re, neg2(s)));
-        re = nr;
-        im = ni;
+// One decimation-in-time butterfly on two register pairs, the same twiddle W = exp(-2 pi i J / 32) in both halves, folded
+// into the additions like bfly_w32 (fft_warp.cuh):  x = a + W b -> LO,  y = a - W b -> HI.
+template <int LO, int HI, int J>
+__device__ __forceinline__ void pk_bfly_dit(Pk& p) {
+    const float2 ar = p.re[LO], ai = p.im[LO], br = p.re[HI], bi = p.im[HI];
+    if constexpr (J == 0) {
+        p.re[LO] = __fadd2_rn(ar, br); p.im[LO] = __fadd2_rn(ai, bi);
+        p.re[HI] = __fadd2_rn(ar, neg2(br)); p.im[HI] = __fadd2_rn(ai, neg2(bi));
+    } else if constexpr (J == 8) {                       // W b = (b.im, -b.re)
+        p.re[LO] = __fadd2_rn(ar, bi); p.im[LO] = __fadd2_rn(ai, neg2(br));
+        p.re[HI] = __fadd2_rn(ar, neg2(bi)); p.im[HI] = __fadd2_rn(ai, br);
+    } else if constexpr (J == 4 || J == 12) {            // W b = r (sm, df) (J = 4), r (df, -sm) (J = 12)
+        const float2 r = dup2((float)kCos32[4]);
+        const float2 sm = __fadd2_rn(br, bi), df = __fadd2_rn(bi, neg2(br));
+        if constexpr (J == 4) {
+            p.re[LO] = __ffma2_rn(r, sm, ar); p.im[LO] = __ffma2_rn(r, df, ai);
+            p.re[HI] = __ffma2_rn(neg2(r), sm, ar); p.im[HI] = __ffma2_rn(neg2(r), df, ai);
+        } else {
+            p.re[LO] = __ffma2_rn(r, df, ar); p.im[LO] = __ffma2_rn(neg2(r), sm, ai);
+            p.re[HI] = __ffma2_rn(neg2(r), df, ar); p.im[HI] = __ffma2_rn(r, sm, ai);
+        }
+    } else {                                             // W = c - i s:  W b = (c b.re + s b.im, c b.im - s b.re)
+        const float2 c = dup2((float)cos32(J)), s = dup2((float)sin32(J)), two = dup2(2.0f);
+        const float2 xr = __ffma2_rn(c, br, __ffma2_rn(s, bi, ar)), xi = __ffma2_rn(c, bi, __ffma2_rn(neg2(s), br, ai));
+        p.re[LO] = xr; p.im[LO] = xi;
+        p.re[HI] = __ffma2_rn(two, ar, neg2(xr)); p.im[HI] = __ffma2_rn(two, ai, neg2(xi));
     }
 }
 
-template <int LO, int HI, int J1, int J2>
-__device__ __forceinline__ void pk_bfly2(Pk& p) {
-    const float2 ar = p.re[LO], ai = p.im[LO], br = p.re[HI], bi = p.im[HI];
-    p.re[LO] = __fadd2_rn(ar, br);
-    p.im[LO] = __fadd2_rn(ai, bi);
-    float2 dr = __fadd2_rn(ar, neg2(br)), di = __fadd2_rn(ai, neg2(bi));
-    pk_mul_w32_2<J1, J2>(dr, di);
-    p.re[HI] = dr;
-    p.im[HI] = di;
-}
-
-// In-register 32-point forward FFT, layout B in -> layout A out (natural order): the radix-2 DIF stages of span
-// 16, 8, 4, 2 act between pairs (element e of a pair and e + 1 take the twiddles W^J and W^(J + 16 / span)), the
-// last stage (span 1) inside each pair.  Pair m ends up holding outputs (brev4(m), brev4(m) + 16).
+// In-register 32-point forward FFT, layout B in -> layout A out (natural order), radix-2 decimation in time.  With
+// t[k] = v[brev5(k)], register pair m holds (t[q], t[q + 16]), q = brev4(m): the stages of span 1, 2, 4, 8 act between
+// register pairs with the SAME twiddle in both halves (trivial twiddles stay trivial), the last stage (span 16) inside each
+// pair, scalar.  Pair m ends up holding outputs (q, q + 16): layout A after a compile-time renaming.
+// 148 packed + 92 scalar instructions (the decimation-in-frequency form it replaces: 256 + 64).
 __device__ __forceinline__ void fft32_ba(Pk& p) {
-    static_for<0, 8>([&](auto ii) { constexpr int m = decltype(ii)::value; pk_bfly2<m, m + 8, 2 * m, 2 * m + 1>(p); });
-    static_for<0, 8>([&](auto ii) {
-        constexpr int i = decltype(ii)::value;
-        constexpr int mm = i % 4, lo = 8 * (i / 4) + mm;
-        pk_bfly2<lo, lo + 4, 4 * mm, 4 * mm + 2>(p);
+    static_for<0, 4>([&](auto ss) {
+        constexpr int S = 1 << decltype(ss)::value;      // span in t-index
+        static_for<0, 8>([&](auto ii) {
+            constexpr int i = decltype(ii)::value;
+            constexpr int k = (i / S) * 2 * S + i % S;   // t-index of the butterfly's first input, k + S the second
+            pk_bfly_dit<brev4(k), brev4(k + S), (i % S) * (16 / S)>(p);
+        });
     });
-    static_for<0, 8>([&](auto ii) {
-        constexpr int i = decltype(ii)::value;
-        constexpr int mm = i % 2, lo = 4 * (i / 2) + mm;
-        pk_bfly2<lo, lo + 2, 8 * mm, 8 * mm + 4>(p);
-    });
-    static_for<0, 8>([&](auto ii) { constexpr int i = decltype(ii)::value; pk_bfly2<2 * i, 2 * i + 1, 0, 8>(p); });
     static_for<0, 16>([&](auto mm) {
-        constexpr int m = decltype(mm)::value;
-        const float2 r = p.re[m], i = p.im[m];
-        p.re[m] = make_float2(r.x + r.y, r.x - r.y);
-        p.im[m] = make_float2(i.x + i.y, i.x - i.y);
+        constexpr int m = decltype(mm)::value, q = brev4(m);
+        float2 x, y;
+        bfly_w32<q>(make_float2(p.re[m].x, p.im[m].x), make_float2(p.re[m].y, p.im[m].y), x, y);
+        p.re[m] = make_float2(x.x, y.x);
+        p.im[m] = make_float2(x.y, y.y);
     });
     Pk t;
     static_for<0, 16>([&](auto aa) { constexpr int a = decltype(aa)::value; t.re[a] = p.re[brev4(a)]; t.im[a] = p.im[brev4(a)]; });
@@ -319,11 +325,13 @@ __device__ __forceinline__ void pk_post_pairs(Pk& p, float* park, const TAB& wp4
             const float2 wy = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
             const float2 zr = p.re[m], zi = p.im[m];
             const float2 er = __fadd2_rn(zr, qr), ei = __fadd2_rn(zi, neg2(qi)), orr = __fadd2_rn(zr, neg2(qr)), oi = __fadd2_rn(zi, qi);
-            const float2 A = __ffma2_rn(wx, orr, __fmul2_rn(neg2(wy), oi)), B = __ffma2_rn(wx, oi, __fmul2_rn(wy, orr));
-            p.re[m] = __fadd2_rn(er, A);
-            p.im[m] = __fadd2_rn(B, ei);
-            p.re[m + 8] = __fadd2_rn(er, neg2(A));
-            p.im[m + 8] = __fadd2_rn(B, neg2(ei));
+            // A = wx orr - wy oi, B = wx oi + wy orr:  X[ka] = (er + A, B + ei),  X[kb] = (er - A, B - ei), folded
+            const float2 two = dup2(2.0f);
+            const float2 xr = __ffma2_rn(wx, orr, __ffma2_rn(neg2(wy), oi, er)), xi = __ffma2_rn(wx, oi, __ffma2_rn(wy, orr, ei));
+            p.re[m] = xr;
+            p.im[m] = xi;
+            p.re[m + 8] = __ffma2_rn(two, er, neg2(xr));
+            p.im[m + 8] = __ffma2_rn(neg2(two), ei, xi);
         });
     });
 }
@@ -340,11 +348,13 @@ __device__ __forceinline__ void pk_pre_pairs(Pk& p, float* park, const TAB& wp4,
         const float2 wy = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
         const float2 xr = p.re[m], xi = p.im[m], rr = p.re[m + 8], ri = p.im[m + 8];
         const float2 er = __fadd2_rn(xr, rr), ei = __fadd2_rn(xi, neg2(ri)), dr = __fadd2_rn(xr, neg2(rr)), di = __fadd2_rn(xi, ri);
-        const float2 C = __ffma2_rn(wx, dr, __fmul2_rn(wy, di));
-        const float2 nD = __ffma2_rn(wy, dr, __fmul2_rn(neg2(wx), di));      // -(wx di - wy dr)
-        p.re[m] = __fadd2_rn(er, C);
-        p.im[m] = __fadd2_rn(nD, neg2(ei));                                   // -(D + ei)
-        const float2 br = __fadd2_rn(er, neg2(C)), bi = __fadd2_rn(ei, nD);   // mirror: (er - C, -(D - ei))
+        // C = wx dr + wy di, D = wx di - wy dr:  own = (er + C, -(D + ei)),  mirror = (er - C, -(D - ei)), folded
+        const float2 two = dup2(2.0f);
+        const float2 yr = __ffma2_rn(wx, dr, __ffma2_rn(wy, di, er));
+        const float2 yi = __ffma2_rn(wy, dr, __ffma2_rn(neg2(wx), di, neg2(ei)));
+        p.re[m] = yr;
+        p.im[m] = yi;
+        const float2 br = __ffma2_rn(two, er, neg2(yr)), bi = __ffma2_rn(two, ei, yi);
         pre[wb + 15 - 2 * m] = br.x; pre[wb + 14 - 2 * m] = br.y;
         pim[wb + 15 - 2 * m] = bi.x; pim[wb + 14 - 2 * m] = bi.y;
       });

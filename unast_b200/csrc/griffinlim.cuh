@@ -62,6 +62,8 @@ struct GlParams {
     GlLink links[GL_MAX_LINKS];
     float2* tprev;               // [sum T][1025] previous STFT estimate (momentum variant) or nullptr
     const float2* angles0;       // [sum T][1025] initial unit phases or nullptr = zero phase
+    const float* frames0;        // zero-phase start only: [sum T][GL_F0_STRIDE] windowed taps 0..551 of w * irfft(S) computed in
+                                 // float64 by gl_init_f64_kernel (tap i == tap 1102 - i), or nullptr
     float alpha;                 // momentum / (1 + momentum); 0 selects classic Griffin-Lim
     const float2* wa2;           // interior frames: (w[2n], w[2n+1]) / 2 / window-sum envelope (periodic part)
     const float2* win2;          // (w[2n], w[2n+1]) / 2
@@ -80,6 +82,7 @@ struct GlParams {
 #define GL_WARPS_N 16
 #endif
 constexpr int GL_WARPS = GL_WARPS_N;
+constexpr int GL_F0_STRIDE = 552;  // floats per frame of GlParams::frames0 (taps 0..551; 2,208 bytes)
 constexpr int GL_XS_BYTES = xs_bytes<float>();                   // 4608: transposition buffer
 constexpr int GL_CARRY = 828;                                     // 827 carried samples + one zero
 

@@ -177,6 +177,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
     for (int it = 0; it <= P.n_iter; ++it) {
         const bool iter_mode = it > 0;                                   // it == 0: inverse transform of S * angles0 only
         const bool first_iter = it == 1;
+        const bool init64 = !iter_mode && P.frames0 != nullptr;          // zero-phase start: taps precomputed in float64
         const float* __restrict__ ola_r = P.ola[it % 3];
         float* __restrict__ ola_w = P.ola[(it + 1) % 3];
         float* __restrict__ ola_z = P.ola[(it + 2) % 3];
@@ -393,6 +394,18 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                     x512i = -2.0f * xs[PK_PARK_PLANE + 32 * PK_PARK_S + 16];
                     gl_update_bin<false>(x512r, x512i, 512, srow, tp, P.alpha, first_iter);
                 }
+            } else if (init64) {
+                // zero-phase start: w * irfft(S) computed in float64 by gl_init_f64_kernel (tap i == tap 1102 - i), in the form
+                // step 5 expects (real parts, negated imaginary parts, unit window)
+                const float* __restrict__ f0 = P.frames0 + (size_t)f * GL_F0_STRIDE;
+                static_for<0, 18>([&](auto jj) {
+                    constexpr int j = decltype(jj)::value;
+                    const int i0 = 2 * (lane + 32 * j);
+                    if (j < 17 || i0 < WIN) {
+                        reB<j>(v) = f0[i0 <= WIN / 2 ? i0 : WIN - i0];
+                        imB<j>(v) = -f0[i0 + 1 <= WIN / 2 ? i0 + 1 : WIN - 1 - i0];
+                    }
+                });
             } else {
                 // initial spectrum S * angles0 in the shifted frame
                 const float2* a0 = P.angles0 ? P.angles0 + (size_t)f * NBINS : nullptr;
@@ -418,19 +431,23 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                 }
             }
             // ---- 4. back to Z' (layout B, in place; mirrors through the park buffer), ISTFT column ----
-            pk_pre_pairs(v, xs, t_wp4, lane);
-            if (lane == 0) { xs[0] = 2.0f * x512r; xs[PK_PARK_PLANE] = 2.0f * x512i; }   // element 16 of lane 0
+            if (!init64) {
+                pk_pre_pairs(v, xs, t_wp4, lane);
+                if (lane == 0) { xs[0] = 2.0f * x512r; xs[PK_PARK_PLANE] = 2.0f * x512i; }   // element 16 of lane 0
+            }
             __syncwarp();
             // next frame's S row (this one has been consumed); after the run's last frame, the first row for the next iteration
             // is fetched at the top of the iteration loop
             if (lane == 0 && f + 1 < f1) tma_load_1d(srow, P.S + (size_t)(f + 1) * S_STRIDE, GLP_SROW_BYTES, bar_s);
-            pk_pre_collect(v, xs, lane);
-            __syncwarp();
             // the next frame's taps go into the transposition buffer as soon as the inverse transform is done with it
             x_staged = iter_mode && f + 1 < f1 && f + 1 < fend && t + 1 >= 4 && t + 1 <= Tb - 5;
-            warp_fft1024_pk_b(v, xs, t_twa, lane, [&]() {
-                if (x_staged && lane == 0) tma_load_1d(xs, ola_r + ((pos0 + HOP) & ~3LL), GLP_X_BYTES, bar_x);
-            });
+            if (!init64) {
+                pk_pre_collect(v, xs, lane);
+                __syncwarp();
+                warp_fft1024_pk_b(v, xs, t_twa, lane, [&]() {
+                    if (x_staged && lane == 0) tma_load_1d(xs, ola_r + ((pos0 + HOP) & ~3LL), GLP_X_BYTES, bar_x);
+                });
+            }
 
             // ---- 5. window, overlap-add with the carried partial sums, emit what became final ----
             // tap i of this frame sits at ola_w[pos0 + i]; taps [0, 275) are complete once this frame is added
@@ -442,7 +459,7 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                 constexpr int j = decltype(jj)::value;
                 const int n = lane + 32 * j;
                 if (j < 17 || n < NLIVE_C) {
-                    const float2 w = s_wini[n];
+                    const float2 w = init64 ? make_float2(1.0f, 1.0f) : s_wini[n];   // float64 start: v already holds the windowed taps
                     const int i0 = 2 * n;
                     float o0 = reB<j>(v) * w.x, o1 = -imB<j>(v) * w.y;
                     if (j < 12 || i0 < OVERLAP) {                            // carry covers taps [0, 827); cb[827] == 0

@@ -4,6 +4,8 @@
 #pragma once
 #include <cfloat>
 #include "common.cuh"
+#include "frontend_pf.cuh"   // rfft_post_pairs (gl_init_f64_kernel)
+#include "griffinlim.cuh"    // GL_F0_STRIDE
 
 namespace unast {
 
@@ -162,6 +164,56 @@ __global__ void gl_prepare_kernel(const float* __restrict__ mag, long long total
         const float m = __fadd_rn(__fsub_rn(__fmul_rn(c, 100.0f), 100.0f), 20.0f);
         const float a = (float)exp10((double)__fmul_rn(m, 0.05f));
         S[r * S_STRIDE + k] = (float)exp2((double)power * log2((double)a));      // a^power; ~1e-15 before the rounding to float
+    }
+}
+
+// K2b: the zero-phase start of utils.griffin_lim (utils.py:311-313: X_best = S, X_t = istft(S)) in float64.
+// irfft of a real, smooth S piles the frame's energy up at sample 0 -- outside the window's support [473, 1575) -- so the
+// taps that survive the window are the ~ -50 dB tail of a large cancellation: a float32 transform leaves them with ~3
+// significant digits, and that one step decides how far the whole 100-iteration run ends from the reference (measured on
+// the CPU: float32 everywhere 56-89 dB, this step alone in float64 101-108 dB; every later step is well conditioned).
+// For real S the inverse is the forward transform of the even extension s[m] = S[min(m, 2048 - m)]:
+//     irfft(S)[n] = X[n] / 2048,  X = rfft(s) real,  and irfft(S)[2048 - n] = irfft(S)[n],
+// so the front end's float64 core (warp_fft1024_split + rfft_post_pairs) does it: one warp per frame, bins 473..1024 -> the
+// windowed taps i = n - 473 = 0..551 (tap 1102 - i is the same value: the periodic Hann window is symmetric too), float32 out.
+struct GlInitParams {
+    const float* S;              // [F][S_STRIDE]
+    long long F;
+    const double2* tw;           // float64 inter-pass twiddles (front end's table)
+    const double2* wp;           // float64 post-processing factors
+    const double* hann;          // [1102] float64 periodic Hann
+    float* frames0;              // [F][GL_F0_STRIDE]
+};
+constexpr int GL_INIT_WARPS = 4;
+__global__ void __launch_bounds__(GL_INIT_WARPS * 32, 3) gl_init_f64_kernel(const GlInitParams P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double* xs = reinterpret_cast<double*>(smem + warp * xs_bytes<double>());
+    for (long long f = (long long)blockIdx.x * GL_INIT_WARPS + warp; f < P.F; f += (long long)gridDim.x * GL_INIT_WARPS) {
+        const float* __restrict__ Sr = P.S + f * S_STRIDE;
+        double2 v[32];                                                   // v[j] = (s[2 n], s[2 n + 1]) / 2, n = lane + 32 j
+        static_for<0, 32>([&](auto jj) {
+            constexpr int j = decltype(jj)::value;
+            const int m = 2 * (lane + 32 * j);
+            if constexpr (j < 16) {
+                const float2 q = *reinterpret_cast<const float2*>(Sr + m);
+                v[j] = mk(0.5 * (double)q.x, 0.5 * (double)q.y);
+            } else {
+                v[j] = mk(0.5 * (double)Sr[2048 - m], 0.5 * (double)Sr[2047 - m]);
+            }
+        });
+        warp_fft1024_split<double, 32>(v, xs, TwMem<double>{P.tw, lane}, lane);
+        float* dst = P.frames0 + f * GL_F0_STRIDE;
+        auto put = [&](int n, double xr) {                               // bin n of X -> tap n - 473
+            const int i = n - WIN_LPAD;
+            if (i >= 0) dst[i] = (float)(xr * (1.0 / NFFT) * P.hann[i]);
+        };
+        rfft_post_pairs<double>(v, reinterpret_cast<double2*>(xs), WpLane<double>{P.wp[lane]}, lane, [&](auto jj, double2 xa, double2 xb) {
+            constexpr int j = decltype(jj)::value;
+            put(lane + 32 * j, xa.x);
+            put(1024 - lane - 32 * j, xb.x);
+        }, [&](double2 x) { put(512, x.x); });
+        __syncwarp();                                                    // the exchange buffers are reused by the next frame
     }
 }
 

@@ -101,6 +101,7 @@ struct unast_ctx {
     float4 *tw4a_f = nullptr, *wp4_f = nullptr;
     float4* tw4_f = nullptr;                                    // tw_f in the packed layout of fft_pk.cuh
     double2 *win2_d = nullptr, *win2i_d = nullptr, *tw_d = nullptr, *wp_d = nullptr;
+    double* hann_d = nullptr;               // float64 periodic Hann (gl_init_f64_kernel)
     float *wss_per = nullptr, *rinv_l = nullptr, *rinv_r = nullptr;
     float2* wa2_f = nullptr;
     double* w2 = nullptr;
@@ -386,6 +387,7 @@ int unast_create(int device, unast_ctx** out) {
     auto up = [&](auto** d, const auto& h) { if (e == cudaSuccess) e = upload(d, h); };
     up(&c->win2_f, win2_f); up(&c->win2i_f, win2i_f); up(&c->wini2_f, wini2_f); up(&c->tw_f, tw_f); up(&c->wp_f, wp_f); up(&c->phi_f, phi_f);
     up(&c->win2_d, win2_d); up(&c->win2i_d, win2i_d); up(&c->tw_d, tw_d); up(&c->wp_d, wp_d);
+    up(&c->hann_d, hann);
     up(&c->tw4_f, tw4_f); up(&c->tw4a_f, tw4a_f); up(&c->wp4_f, wp4_f);
     up(&c->wa2_f, wa2_f); up(&c->rinv_l, rinv_l); up(&c->rinv_r, rinv_r);
     up(&c->it_w, it_w); up(&c->it_k0, it_k0); up(&c->it_mel, it_mel);
@@ -417,7 +419,7 @@ int unast_destroy(unast_ctx* c) {
     if (!c) return UNAST_OK;
     DeviceGuard guard(c->device);
     cudaFree(c->win2_f); cudaFree(c->win2i_f); cudaFree(c->win2i_d); cudaFree(c->wini2_f); cudaFree(c->tw_f); cudaFree(c->wp_f); cudaFree(c->phi_f);
-    cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d);
+    cudaFree(c->win2_d); cudaFree(c->tw_d); cudaFree(c->wp_d); cudaFree(c->hann_d);
     cudaFree(c->tw4_f); cudaFree(c->tw4a_f); cudaFree(c->wp4_f);
     cudaFree(c->wa2_f); cudaFree(c->rinv_l); cudaFree(c->rinv_r);
     cudaFree(c->it_w); cudaFree(c->it_k0); cudaFree(c->it_mel);
@@ -529,6 +531,7 @@ struct GlPlan {
     std::vector<long long> pad_off, cost_off;
     long long total_frames = 0, total_pad = 0;
     size_t o_runs = 0, o_meta_i = 0, o_meta_l = 0, o_sync = 0, o_mail = 0, o_S = 0, o_ola = 0, ola_stride = 0, o_tprev = 0, o_be = 0, bytes = 0;
+    size_t o_f0 = 0;
 };
 // edge frames (reflect padding, envelope tables) cost 5, interior frames 4
 void frag_edges(int t0, int n, int Tg, int& head, int& tail) {
@@ -562,6 +565,7 @@ bool gl_plan(const int32_t* frames, const int32_t* t0, const int32_t* tglob, int
     p.o_ola = o; o += 3 * p.ola_stride;
     p.o_tprev = o; if (momentum != 0.f) o += align256((size_t)p.total_frames * NBINS * sizeof(float2));
     p.o_be = o; o += align256((size_t)B * ((max_wav + TRIM_HOP - 1) / TRIM_HOP) * sizeof(double));
+    p.o_f0 = o; o += align256((size_t)p.total_frames * GL_F0_STRIDE * sizeof(float));
     p.bytes = o;
     return true;
 }
@@ -638,6 +642,15 @@ int gl_run(unast_ctx* c, const float* mag_norm, const GlPlan& p, int B, const un
     CU(cudaMemsetAsync(c->d_abort, 0, sizeof(int), st));
     gl_prepare_kernel<<<c->num_sms * 8, 256, 0, st>>>(mag_norm, p.total_frames, power, S);
 
+    float* frames0 = nullptr;
+    if (!angles0) {                                                      // zero-phase start: the ill-conditioned first inverse in float64
+        frames0 = (float*)(ws + p.o_f0);
+        GlInitParams I;
+        I.S = S; I.F = p.total_frames; I.tw = c->tw_d; I.wp = c->wp_d; I.hann = c->hann_d; I.frames0 = frames0;
+        const int grid = (int)std::min<long long>((p.total_frames + GL_INIT_WARPS - 1) / GL_INIT_WARPS, (long long)c->num_sms * 3);
+        gl_init_f64_kernel<<<grid, GL_INIT_WARPS * 32, GL_INIT_WARPS * xs_bytes<double>(), st>>>(I);
+    }
+
     GlParams P;
     memset(&P, 0, sizeof(P));
     P.S = S; P.frame_off = d.frame_off; P.pad_off = d.pad_off; P.t0 = d.t0; P.Tg = d.Tg; P.B = B;
@@ -647,6 +660,7 @@ int gl_run(unast_ctx* c, const float* mag_norm, const GlPlan& p, int B, const un
     P.n_iter = n_iter; P.done = (int*)(ws + p.o_sync); P.epoch = epoch; P.abort = c->d_abort; P.err = c->d_err;
     P.tprev = momentum != 0.f ? (float2*)(ws + p.o_tprev) : nullptr;
     P.angles0 = (const float2*)angles0;
+    P.frames0 = frames0;
     P.alpha = momentum / (1.0f + momentum);
     P.wa2 = c->wa2_f; P.win2 = c->win2_f; P.wini2 = c->wini2_f; P.tw4 = c->tw4_f; P.tw4a = c->tw4a_f; P.wp4 = c->wp4_f; P.phi = c->phi_f;
     P.rinv_l = c->rinv_l; P.rinv_r = c->rinv_r; P.wss_per = c->wss_per; P.w2 = c->w2;

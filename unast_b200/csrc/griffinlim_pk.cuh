@@ -522,6 +522,14 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
             st_release_gpu(P.done + gw, P.epoch + it + 1);
         }
     }
+    // Linked seams: the partner's partial sums of the LAST iteration land in this side's buffer from another launch (another
+    // GPU): what follows this kernel on the stream (extraction, de-emphasis) may only run once they are there.  (Seams between
+    // runs of this launch are complete when the kernel is.)
+    if (!dead && (link_l >= 0 || link_r >= 0)) {
+        bool ok = true;
+        if (link_l >= 0) ok = gl_wait<true>(poll_l, P.epoch + P.n_iter + 1, P.abort, P.err, lane);
+        if (ok && link_r >= 0) ok = gl_wait<true>(poll_r, P.epoch + P.n_iter + 1, P.abort, P.err, lane);
+    }
     tmem_fence_before_sync();
     asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");
     if (warp == 0) tmem_dealloc(*s_tmem, GLT_COLS);

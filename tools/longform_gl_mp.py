@@ -22,7 +22,7 @@ eng = U.get_engine()
 w = np.concatenate([synth.speech_like(10.0, 80 + i) for i in range((secs + 9) // 10)])[:secs * 22050]
 (mel, mag), = U.spectrograms_from_waves([w], do_trim=False)
 T = mag.shape[0]
-sh = LF.ShardedGriffinLim(T, rank, world)
+sh = LF.ShardedGriffinLim(T, rank, world, canonical=False)        # the speed-optimised cut
 rows = torch.from_numpy(np.ascontiguousarray(mag[sh.a:sh.b])).cuda()
 raw = sh.run(rows, iters)
 eng.check()

@@ -23,6 +23,7 @@ namespace unast {
 #endif
 
 constexpr int AU_ROW = 1032;                 // floats per |X| row: bins 0..1024 + zero padding up to the last item's end
+constexpr int AU_MEL_CAP0 = 2, AU_MEL_CAP1 = 6, AU_MEL_CAP2 = 12;   // most items of a mel in 0..31 / 32..63 / 64..79 (checked by the host)
 constexpr int AU_BATCH = 5;                  // rounds per batch; the host pads the tables to a multiple of it
 constexpr int AU_MAX_ROUNDS = 15;
 
@@ -244,16 +245,35 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
             }
         }
         __syncwarp();
+        {
+            // The mels, in item order: lane l sums mels l, l + 32 and (l < 16) l + 64.  All item sums of the three are fetched
+            // first (predicated 32-bit loads, at most AU_MEL_CAP* each: the host checks the plan against the caps), so the
+            // shared-memory latency is paid once per frame instead of once per item; adding 0 for an absent item leaves the
+            // sum unchanged, so the result is the sequential sum of the mel's items.
+            const int2 i0 = s_mel[lane], i1 = s_mel[lane + 32], i2 = lane < NMELS - 64 ? s_mel[lane + 64] : make_int2(0, 0);
+            float q0[AU_MEL_CAP0], q1[AU_MEL_CAP1], q2[AU_MEL_CAP2];
 #pragma unroll
-        for (int m = lane; m < NMELS; m += 32) {
-            const int2 it = s_mel[m];
-            const int nmax = __reduce_max_sync(__activemask(), it.y);     // warp-uniform trip count, predicated adds
-            float s = partial[it.x];
-            for (int i = 1; i < nmax; ++i) { const float q = partial[it.x + min(i, it.y - 1)]; s += i < it.y ? q : 0.0f; }
-            const float val = db_norm(s);
-            const int fbase = st[3], t = st[0] - fbase;
-            if (P.mel_layout == 0) P.mel_out[(size_t)NMELS * fbase + (size_t)m * (st[2] - fbase) + t] = val;
-            else P.mel_out[((size_t)st[5] * P.T_max + t) * NMELS + m] = val;
+            for (int i = 0; i < AU_MEL_CAP0; ++i) q0[i] = i < i0.y ? partial[i0.x + i] : 0.0f;
+#pragma unroll
+            for (int i = 0; i < AU_MEL_CAP1; ++i) q1[i] = i < i1.y ? partial[i1.x + i] : 0.0f;
+#pragma unroll
+            for (int i = 0; i < AU_MEL_CAP2; ++i) q2[i] = i < i2.y ? partial[i2.x + i] : 0.0f;
+            float s0 = q0[0], s1 = q1[0], s2 = q2[0];
+#pragma unroll
+            for (int i = 1; i < AU_MEL_CAP0; ++i) s0 += q0[i];
+#pragma unroll
+            for (int i = 1; i < AU_MEL_CAP1; ++i) s1 += q1[i];
+#pragma unroll
+            for (int i = 1; i < AU_MEL_CAP2; ++i) s2 += q2[i];
+            const int fbase = st[3], t = st[0] - fbase, Tu = st[2] - fbase, bu = st[5];
+            auto put = [&](int m, float sum) {
+                const float val = db_norm(sum);
+                if (P.mel_layout == 0) P.mel_out[(size_t)NMELS * fbase + (size_t)m * Tu + t] = val;
+                else P.mel_out[((size_t)bu * P.T_max + t) * NMELS + m] = val;
+            };
+            put(lane, s0);
+            put(lane + 32, s1);
+            if (lane < NMELS - 64) put(lane + 64, s2);
         }
         __syncwarp();                                                     // partial sums read before xs is reused
         if (lane == 0) st[0] = st[0] + 1;

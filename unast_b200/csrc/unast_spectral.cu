@@ -369,6 +369,8 @@ int unast_create(int device, unast_ctx** out) {
             if (lo < 0) { items.push_back({m, 0}); it_mel[m].y = 1; continue; }     // empty filter: one all-zero item
             for (int k0 = lo & ~3; k0 <= hi; k0 += 8) { items.push_back({m, k0}); ++it_mel[m].y; }
         }
+        for (int m = 0; m < NMELS; ++m)
+            if (it_mel[m].y > (m < 32 ? AU_MEL_CAP0 : m < 64 ? AU_MEL_CAP1 : AU_MEL_CAP2)) { delete c; return fail(UNAST_E_ARG, "unast_create: filterbank item plan exceeds AU_MEL_CAP"); }
         const int rounds = (((int)items.size() + 31) / 32 + AU_BATCH - 1) / AU_BATCH * AU_BATCH;
         if (rounds > AU_MAX_ROUNDS) { delete c; return fail(UNAST_E_ARG, "unast_create: filterbank item plan exceeds AU_MAX_ROUNDS"); }
         it_w.assign((size_t)rounds * 64, make_float4(0.f, 0.f, 0.f, 0.f));

@@ -52,6 +52,7 @@ struct FeAuLayout {
     static constexpr int bytes = off_state + FW * 32 + 16;               // + the TMEM base address word
     static_assert(XCH_BYTES >= AU_MAX_ROUNDS * 32 * 4, "partial sums live in the idle exchange buffer");
     static_assert(bytes <= 227 * 1024, "shared memory budget");
+    static_assert(off_state % 16 == 0, "the loop state is read with 128-bit loads");
 };
 
 template <class T, int FW>
@@ -152,22 +153,30 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
 
     float* partial = reinterpret_cast<float*>(xs);                        // item sums: the exchange buffer is idle then
 #pragma unroll 1
+    // the eight state words in two 128-bit loads: one shared-memory latency at the top of a frame instead of a chain of them
+    auto ld_state = [&](int4& a, int4& b2) {
+        const uint32_t sp = smem_u32(const_cast<int*>(st));
+        asm volatile("ld.volatile.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "r"(sp) : "memory");
+        asm volatile("ld.volatile.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(b2.x), "=r"(b2.y), "=r"(b2.z), "=r"(b2.w) : "r"(sp + 16) : "memory");
+    };
     for (;;) {
-        {
-            const int f = st[0];
-            if (f >= st[1]) break;
-            if (f >= st[2]) {                                             // the run crosses into the next utterance
-                __syncwarp();
-                if (lane == 0) { int bb = st[5]; do { ++bb; } while (f >= P.frame_off[bb + 1]); utt(bb); }
-                __syncwarp();
-            }
+        int4 sa, sb;                                                      // (f, fb, fend, fbase), (N, b, wbase lo, wbase hi)
+        ld_state(sa, sb);
+        if (sa.x >= sa.y) break;
+        if (sa.x >= sa.z) {                                               // the run crosses into the next utterance
+            __syncwarp();
+            if (lane == 0) { int bb = sb.y; do { ++bb; } while (sa.x >= P.frame_off[bb + 1]); utt(bb); }
+            __syncwarp();
+            ld_state(sa, sb);
         }
         C v[32];
         {
-            const int t = st[0] - st[3];
-            const int N = st[4];
-            const long long wbase = wbase_of();
-            if (prefetched(t)) {
+            const int t = sa.x - sa.w;
+            const int N = sb.x;
+            const long long wbase = (long long)(((unsigned long long)(unsigned)sb.w << 32) | (unsigned)sb.z);
+            const bool pf_now = P.wave_is_i16 && pf_interior(t, N);
+            const bool pf_next = sa.x + 1 < sa.y && sa.x + 1 < sa.z && P.wave_is_i16 && pf_interior(t + 1, N);
+            if (pf_now) {
                 cp_async_wait_all();
                 __syncwarp();
                 const long long A = wbase + (HOP * t + WIN_LPAD - HALF) - 1;
@@ -181,8 +190,7 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
             }
             // next frame of the same utterance: its samples land while this one is transformed (the first frames of
             // an utterance are edge frames and never prefetched, so nothing is lost at a boundary)
-            const int f1 = st[0] + 1;
-            if (f1 < st[1] && f1 < st[2] && prefetched(t + 1)) pf_issue(P.wave, wbase, t + 1, stage, lane);
+            if (pf_next) pf_issue(P.wave, wbase, t + 1, stage, lane);
         }
 
         if constexpr (TW_TMEM) warp_fft1024_split<T, 18>(v, xs, TwTmemF64{tq}, lane);
@@ -222,11 +230,18 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
         // ---- filterbank: items of 8 bins, then the mels in item order ----
         // batches of AU_BATCH rounds: all addresses, then all 128-bit loads, then two FMA chains per item -- the
         // shared-memory latency of one batch is paid once, not once per item
+        int k0n[AU_BATCH];                                                // the first bins of the next batch's items, one batch ahead
+#pragma unroll
+        for (int i = 0; i < AU_BATCH; ++i) k0n[i] = s_k0[i * 32 + lane];
 #pragma unroll 1
         for (int r0 = 0; r0 < rounds; r0 += AU_BATCH) {
             int k0[AU_BATCH];
 #pragma unroll
-            for (int i = 0; i < AU_BATCH; ++i) k0[i] = s_k0[(r0 + i) * 32 + lane];
+            for (int i = 0; i < AU_BATCH; ++i) k0[i] = k0n[i];
+            if (r0 + AU_BATCH < rounds) {
+#pragma unroll
+                for (int i = 0; i < AU_BATCH; ++i) k0n[i] = s_k0[(r0 + AU_BATCH + i) * 32 + lane];
+            }
             float4 x0[AU_BATCH], x1[AU_BATCH], w0[AU_BATCH], w1[AU_BATCH];
 #pragma unroll
             for (int i = 0; i < AU_BATCH; ++i) {

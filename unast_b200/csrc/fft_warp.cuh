@@ -196,19 +196,30 @@ struct TwMem {
 };
 struct TwTmemF64 {
     uint32_t base;                                   // lane quadrant | column of row 0
+    // four twiddles per tcgen05.ld, the next four in flight while the current ones are used
     __device__ __forceinline__ void apply(double2 (&v)[32]) const {
+        uint32_t a[16], b[16];
+        tmem_ld16(base, a);
         static_for<0, 8>([&](auto cc) {
             constexpr int c = decltype(cc)::value;
-            uint32_t r[16];
-            tmem_ld16(base + 16 * c, r);
-            tmem_wait16(r);
-            static_for<0, 4>([&](auto ii) {
-                constexpr int k1 = 4 * c + decltype(ii)::value, i = decltype(ii)::value;
-                if constexpr (k1 > 0) {
-                    const double wx = __hiloint2double((int)r[4 * i + 1], (int)r[4 * i]), wy = __hiloint2double((int)r[4 * i + 3], (int)r[4 * i + 2]);
-                    v[k1] = cmul(v[k1], make_double2(wx, wy));
-                }
-            });
+            auto use = [&](uint32_t (&r)[16]) {
+                static_for<0, 4>([&](auto ii) {
+                    constexpr int k1 = 4 * c + decltype(ii)::value, i = decltype(ii)::value;
+                    if constexpr (k1 > 0) {
+                        const double wx = __hiloint2double((int)r[4 * i + 1], (int)r[4 * i]), wy = __hiloint2double((int)r[4 * i + 3], (int)r[4 * i + 2]);
+                        v[k1] = cmul(v[k1], make_double2(wx, wy));
+                    }
+                });
+            };
+            if constexpr (c % 2 == 0) {
+                tmem_wait16(a);
+                if constexpr (c + 1 < 8) tmem_ld16(base + 16 * (c + 1), b);
+                use(a);
+            } else {
+                tmem_wait16(b);
+                if constexpr (c + 1 < 8) tmem_ld16(base + 16 * (c + 1), a);
+                use(b);
+            }
         });
     }
 };

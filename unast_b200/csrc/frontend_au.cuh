@@ -197,8 +197,8 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
         else warp_fft1024_split<T, 18>(v, xs, TwMem<T>{s_tw, lane}, lane);
 
         float* mrow = P.mag_out ? P.mag_out + (size_t)st[0] * NBINS : nullptr;
+        float pa[16], pb[16], p512 = 0.0f;
         {
-            float pa[16], pb[16], p512 = 0.0f;
             rfft_post_pairs<T>(v, reinterpret_cast<C*>(xs), wp, lane, [&](auto jj, C xa, C xb) {
                 constexpr int j = decltype(jj)::value;
                 const float ar = (float)xa.x, ai = (float)xa.y;          // complex64 storage of librosa.stft
@@ -214,27 +214,16 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
                 rowb[-32 * j] = sqrt_approx(pb[j]);
             });
             if (lane == 0) row[512] = sqrt_approx(p512);
-            if (mrow) {
-                float* ma = mrow + lane;
-                float* mb = mrow + 1024 - lane;
-                static_for<0, 16>([&](auto jj) {
-                    constexpr int j = decltype(jj)::value;
-                    ma[32 * j] = db_norm_pw_nf(pa[j]);
-                    mb[-32 * j] = db_norm_pw_nf(pb[j]);
-                });
-                if (lane == 0) mrow[512] = db_norm_pw_nf(p512);
-            }
         }
-        __syncwarp();                                                     // row complete; park buffer reads done
-
         // ---- filterbank: items of 8 bins, then the mels in item order ----
         // batches of AU_BATCH rounds: all addresses, then all 128-bit loads, then two FMA chains per item -- the
         // shared-memory latency of one batch is paid once, not once per item
         int k0n[AU_BATCH];                                                // the first bins of the next batch's items, one batch ahead
 #pragma unroll
         for (int i = 0; i < AU_BATCH; ++i) k0n[i] = s_k0[i * 32 + lane];
-#pragma unroll 1
-        for (int r0 = 0; r0 < rounds; r0 += AU_BATCH) {
+        __syncwarp();                                                     // row complete; park buffer reads done
+        float4 x0[AU_BATCH], x1[AU_BATCH], w0[AU_BATCH], w1[AU_BATCH];
+        auto fb_loads = [&](int r0) {
             int k0[AU_BATCH];
 #pragma unroll
             for (int i = 0; i < AU_BATCH; ++i) k0[i] = k0n[i];
@@ -242,7 +231,6 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
 #pragma unroll
                 for (int i = 0; i < AU_BATCH; ++i) k0n[i] = s_k0[(r0 + AU_BATCH + i) * 32 + lane];
             }
-            float4 x0[AU_BATCH], x1[AU_BATCH], w0[AU_BATCH], w1[AU_BATCH];
 #pragma unroll
             for (int i = 0; i < AU_BATCH; ++i) {
                 x0[i] = *reinterpret_cast<const float4*>(row + k0[i]);
@@ -250,6 +238,8 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
                 w0[i] = s_w[(r0 + i) * 64 + lane];
                 w1[i] = s_w[(r0 + i) * 64 + 32 + lane];
             }
+        };
+        auto fb_fmas = [&](int r0) {
 #pragma unroll
             for (int i = 0; i < AU_BATCH; ++i) {
                 float a = x0[i].x * w0[i].x, c = x1[i].x * w1[i].x;
@@ -258,6 +248,24 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
                 a = fmaf(x0[i].w, w0[i].w, a); c = fmaf(x1[i].w, w1[i].w, c);
                 partial[(r0 + i) * 32 + lane] = a + c;
             }
+        };
+        fb_loads(0);
+        // the normalised magnitudes go out while the first batch of the filterbank is on its way from shared memory
+        if (mrow) {
+            float* ma = mrow + lane;
+            float* mb = mrow + 1024 - lane;
+            static_for<0, 16>([&](auto jj) {
+                constexpr int j = decltype(jj)::value;
+                ma[32 * j] = db_norm_pw_nf(pa[j]);
+                mb[-32 * j] = db_norm_pw_nf(pb[j]);
+            });
+            if (lane == 0) mrow[512] = db_norm_pw_nf(p512);
+        }
+        fb_fmas(0);
+#pragma unroll 1
+        for (int r0 = AU_BATCH; r0 < rounds; r0 += AU_BATCH) {
+            fb_loads(r0);
+            fb_fmas(r0);
         }
         __syncwarp();
         {

@@ -152,13 +152,13 @@ __global__ void __launch_bounds__(FW * 32, 1) frontend_au_kernel(const FrontendP
     if (prefetched(fa - st[3])) pf_issue(P.wave, wbase_of(), fa - st[3], stage, lane);
 
     float* partial = reinterpret_cast<float*>(xs);                        // item sums: the exchange buffer is idle then
-#pragma unroll 1
     // the eight state words in two 128-bit loads: one shared-memory latency at the top of a frame instead of a chain of them
     auto ld_state = [&](int4& a, int4& b2) {
         const uint32_t sp = smem_u32(const_cast<int*>(st));
         asm volatile("ld.volatile.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "r"(sp) : "memory");
         asm volatile("ld.volatile.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(b2.x), "=r"(b2.y), "=r"(b2.z), "=r"(b2.w) : "r"(sp + 16) : "memory");
     };
+#pragma unroll 1
     for (;;) {
         int4 sa, sb;                                                      // (f, fb, fend, fbase), (N, b, wbase lo, wbase hi)
         ld_state(sa, sb);

@@ -154,7 +154,8 @@ class SpectralEngine:
         bounds = torch.empty((B, 2), dtype=torch.int32, device=self.device) if want_trim else None
         L.check(self.lib.unast_griffinlim(self.h, _ptr(mag_norm), fptr, B, int(n_iter), float(momentum), _ptr(a0), float(power),
                                           1 if deemphasis else 0, _ptr(wav_out), _ptr(bounds), _ptr(ws), nbytes, self._stream()))
-        self.launches += 3 + (2 if want_trim else 0)        # prepare, ONE persistent Griffin-Lim launch, de-emphasis (+ trim)
+        # prepare, (zero-phase start: the float64 first inverse,) ONE persistent Griffin-Lim launch, de-emphasis (+ trim)
+        self.launches += 3 + (1 if angles0 is None else 0) + (2 if want_trim else 0)
         return wav_out, wav_off, bounds
 
     # -- sharded long-form Griffin-Lim ------------------------------------------
@@ -213,7 +214,7 @@ class SpectralEngine:
                                                     tga.ctypes.data_as(C.c_void_p), B, C.cast(arr, C.c_void_p), len(links), int(epoch),
                                                     int(n_iter), float(momentum), _ptr(a0), float(power), _ptr(raw_out), ws_ptr, nbytes,
                                                     self._stream()))
-        self.launches += 3
+        self.launches += 3 + (1 if angles0 is None else 0)
         return raw_out, raw_off
 
     def deemph_trim(self, x, offsets, max_len, deemphasis=True, want_trim=True):

@@ -154,8 +154,12 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
     const int link_l = (run.w & 0xffff) - 1, link_r = (run.w >> 16) - 1;
     // whose progress this warp waits for, and whom it tells its own: the owners of the adjacent runs, or the partner
     // of a linked seam through the mailboxes
-    const int* poll_l = link_l >= 0 ? P.links[link_l].poll : (gw > 0 ? P.done + gw - 1 : nullptr);
-    const int* poll_r = link_r >= 0 ? P.links[link_r].poll : (gw + 1 < P.n_runs ? P.done + gw + 1 : nullptr);
+    // Inside a CTA the barrier at the start of every iteration already says that both neighbours have finished the previous one
+    // (every warp publishes, fences and then arrives): only the first and the last warp of a CTA poll a counter -- their neighbour
+    // lives in another CTA -- and only their counters are ever read.
+    const bool cta_first = warp == 0, cta_last = 32 * (warp + 1) == cta_threads;
+    const int* poll_l = link_l >= 0 ? P.links[link_l].poll : (gw > 0 && cta_first ? P.done + gw - 1 : nullptr);
+    const int* poll_r = link_r >= 0 ? P.links[link_r].poll : (gw + 1 < P.n_runs && cta_last ? P.done + gw + 1 : nullptr);
     uint32_t ph_s = 0, ph_x = 0;                                         // mbarrier phases
 
     if (link_l >= 0 || link_r >= 0) {
@@ -518,8 +522,8 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 1) gl_persist_kernel(const GlPa
                 if (link_l >= 0) st_release_sys(P.links[link_l].push, P.epoch + it + 1);
                 if (link_r >= 0) st_release_sys(P.links[link_r].push, P.epoch + it + 1);
             }
-            __threadfence();
-            st_release_gpu(P.done + gw, P.epoch + it + 1);
+            __threadfence();                                             // (also what makes this warp's sums visible behind the CTA barrier)
+            if (cta_first || cta_last) st_release_gpu(P.done + gw, P.epoch + it + 1);
         }
     }
     // Linked seams: the partner's partial sums of the LAST iteration land in this side's buffer from another launch (another

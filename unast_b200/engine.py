@@ -269,7 +269,14 @@ class SpectralEngine:
         """mel_augment for callers that must not allocate (include/unast_spectral.h: unast_mel_augment_static): `out` is
         required, the scratch is the library's file-scope device array (B <= 1024), no torch or CUDA allocation happens here.
         Calls that overlap on the GPU share that array and race."""
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.dim() != 3 or out.dtype != torch.float32 or not out.is_contiguous() \
+                or out.shape != x.shape:
+            raise TypeError("x and out must be contiguous float32 [B, T, D] tensors of the same shape")
         B, T, D = (int(v) for v in x.shape)
+        if spans is not None and (spans.dtype != torch.int32 or tuple(spans.shape) != (B, 4) or not spans.is_contiguous()):
+            raise TypeError("spans must be a contiguous int32 [B, 4] tensor")
+        if keep is not None and (keep.dtype != torch.float32 or tuple(keep.shape) != (B, T) or not keep.is_contiguous()):
+            raise TypeError("keep must be a contiguous float32 [B, T] tensor")
         L.check(self.lib.unast_mel_augment_static(self.h, _ptr(x), B, T, D, _ptr(spans), _ptr(keep), 1 if replace_with_zero else 0,
                                                   _ptr(out), self._stream()))
         self.launches += 2 if (spans is not None and not replace_with_zero) else 1

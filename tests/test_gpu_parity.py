@@ -137,12 +137,27 @@ def test_frontend_without_trim_and_minimum_length():
 
 def test_frontend_edge_cases_raise():
     from unast_b200 import utils as U
-    from unast_b200._lib import UnastError
     assert U.spectrograms_from_waves([]) == []
     with pytest.raises(IndexError):
         U.spectrograms_from_waves([np.zeros(0, np.float32)])                     # utils.py:251 raises on empty audio
-    with pytest.raises(UnastError):
-        U.spectrograms_from_waves([np.ones(600, np.float32)])                    # too short for reflect padding
+
+
+def test_frontend_short_clips_are_reflected_like_numpy_pad():
+    """Clips of <= 1024 samples: numpy.pad(mode="reflect") reflects them more than once inside librosa's 1024-sample padding
+    (stft and effects.trim alike); the drop-in does the same instead of refusing them."""
+    from unast_b200 import synth, utils as U
+    rng = np.random.RandomState(9)
+    waves = [0.1 * rng.randn(n).astype(np.float32) for n in (2, 3, 275, 300, 600, 1023, 1024)] + [np.ones(600, np.float32)]
+    for do_trim in (False, True):
+        res = U.spectrograms_from_waves(waves, do_trim=do_trim, return_bounds=True)
+        for w, (mel, mag, b) in zip(waves, res):
+            omel, omag, ob = so.spectrograms_from_wave(w, do_trim=do_trim, return_bounds=True)
+            assert b == ob and mel.shape == omel.shape and mag.shape == omag.shape, (w.size, b, ob)
+            assert np.abs(mag - omag).max() <= TOL and np.abs(mel - omel).max() <= TOL, w.size
+    pcm = [synth.to_pcm16(w) for w in waves[2:7]]                                  # the int16 path too
+    for w, (mel, mag) in zip(pcm, U.spectrograms_from_waves(pcm, do_trim=False)):
+        omel, omag = so.spectrograms_from_wave(w.astype(np.float32) / np.float32(32768.0), do_trim=False)
+        assert np.abs(mag - omag).max() <= TOL and np.abs(mel - omel).max() <= TOL
 
 
 def test_frontend_padded_loader_layout(engine):

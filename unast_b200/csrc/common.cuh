@@ -146,6 +146,16 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
                  : "memory");
 }
 
+// numpy.pad(..., mode="reflect") index: position m of the infinitely reflected signal of length N (period 2 (N - 1); N == 1: constant)
+__device__ __forceinline__ int reflect_index(int m, int N) {
+    if (m >= 0 && m < N) return m;
+    if (N == 1) return 0;
+    const int P = 2 * (N - 1);
+    m %= P;
+    if (m < 0) m += P;
+    return m < N ? m : P - m;
+}
+
 // ---- progress counters between warps (same GPU: .gpu scope; another GPU over NVLink: .sys scope) ------------------
 __device__ __forceinline__ int ld_acquire_sys(const int* p) {
     int v;
@@ -220,7 +230,7 @@ __device__ __forceinline__ float wss_at(int q, int T, const float* __restrict__ 
 // Error word layout shared by all kernels (unast_ctx::d_err): first non-zero code wins.
 enum DevErr : int {
     ERR_NONE = 0,
-    ERR_TOO_SHORT = 1,     // an utterance is too short for reflect padding (librosa would raise too)
+    ERR_TOO_SHORT = 1,     // (no longer raised by the front end: short clips are reflect-padded repeatedly, like numpy.pad)
     ERR_EMPTY = 2,         // trimmed signal is empty (reference: IndexError at utils.py:251)
     ERR_SYNC = 3,          // a neighbour wait of the persistent Griffin-Lim kernel timed out (a peer rank never arrived)
 };

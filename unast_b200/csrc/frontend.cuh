@@ -115,7 +115,7 @@ __device__ __forceinline__ void load_frame(cplx_t<T> (&v)[32], const void* __res
     } else {
         // edge frame: reflect padding of librosa.stft(center=True); y[0] = x[0] (np.append(y[0], ...), utils.py:251)
         auto sample = [&](int m) -> float {                    // pre-emphasised signal at (reflected) index m
-            if (m < 0) m = -m; else if (m >= N) m = 2 * (N - 1) - m;
+            m = reflect_index(m, N);                              // (clips of <= 1024 samples are reflected more than once)
             float cur, prev = 0.0f;
             if constexpr (I16) {
                 const short* s = reinterpret_cast<const short*>(wave) + wbase;

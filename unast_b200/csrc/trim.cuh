@@ -47,16 +47,34 @@ __global__ void __launch_bounds__(128) trim_decide_kernel(const void* wave, int 
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long base = off[b];
     const int N = (int)(off[b + 1] - base);
-    if (N <= TRIM_FRAME / 2) {                       // np.pad(..., 'reflect') needs N > 1024
-        if (tid == 0) { bounds[2 * b] = 0; bounds[2 * b + 1] = 0; atomicCAS(err, ERR_NONE, ERR_TOO_SHORT); }
+    if (N <= 0) {
+        if (tid == 0) { bounds[2 * b] = 0; bounds[2 * b + 1] = 0; }     // (unast_frame_offsets reports the empty utterance)
         return;
     }
     const int nfr = 1 + N / TRIM_HOP;
+    // Clips of <= 1024 samples: numpy reflects them more than once inside the 1024-sample padding; the block decomposition
+    // below assumes a single reflection, so their (at most three) frames are summed directly.
+    __shared__ double s_small[3];
+    const bool small = N <= TRIM_FRAME / 2;
+    if (small) {
+        for (int i = 0; i < nfr; ++i) {
+            double part = 0.0;
+            for (int k = tid; k < TRIM_FRAME; k += 128) {
+                const double y = ld_sample(wave, is_i16, base + reflect_index(TRIM_HOP * i - TRIM_FRAME / 2 + k, N));
+                part += y * y;
+            }
+            part = warp_sum(part);
+            if (lane == 0) s_red[warp] = part;
+            __syncthreads();
+            if (tid == 0) s_small[i] = s_red[0] + s_red[1] + s_red[2] + s_red[3];
+            __syncthreads();
+        }
+    }
     const double* beb = be + (size_t)b * nblk_max;
 
     // reflected contributions exist only for frames 0, 1 (left) and the last <= 3 frames (right):
     // slots 0,1 = left part of frames 0,1; slots 2..4 = right part of frames nfr-3 .. nfr-1
-    for (int e = 0; e < 5; ++e) {
+    for (int e = 0; e < 5 && !small; ++e) {
         int i, lo, hi;                               // reflected source range [lo, hi] (inclusive) of frame i
         if (e < 2) { i = e; lo = 1; hi = TRIM_FRAME / 2 - TRIM_HOP * i; }
         else {
@@ -76,6 +94,7 @@ __global__ void __launch_bounds__(128) trim_decide_kernel(const void* wave, int 
     }
 
     auto frame_energy = [&](int i) -> double {
+        if (small) return s_small[i];
         const int lo = max(0, TRIM_HOP * i - TRIM_FRAME / 2), hi = min(N, TRIM_HOP * i + TRIM_FRAME / 2);
         double e = 0.0;
         for (int j = lo / TRIM_HOP; j * TRIM_HOP < hi; ++j) e += beb[j];
@@ -126,7 +145,6 @@ __global__ void __launch_bounds__(1024) frame_offsets_kernel(const int* __restri
         if (b < B) {
             const int N = bounds[2 * b + 1] - bounds[2 * b];
             if (N <= 0) atomicCAS(err, ERR_NONE, ERR_EMPTY);
-            else if (N <= HALF) atomicCAS(err, ERR_NONE, ERR_TOO_SHORT);
             else T = 1 + N / HOP;
         }
         int x = T;

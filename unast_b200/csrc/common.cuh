@@ -146,14 +146,12 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
                  : "memory");
 }
 
-// numpy.pad(..., mode="reflect") index: position m of the infinitely reflected signal of length N (period 2 (N - 1); N == 1: constant)
+// numpy.pad(..., mode="reflect") index: position m of the infinitely reflected signal of length N (period 2 (N - 1); N == 1: constant).
+// A loop of single reflections: one pass for every clip of more than 1024 samples, no integer division, no call.
 __device__ __forceinline__ int reflect_index(int m, int N) {
-    if (m >= 0 && m < N) return m;
     if (N == 1) return 0;
-    const int P = 2 * (N - 1);
-    m %= P;
-    if (m < 0) m += P;
-    return m < N ? m : P - m;
+    while (m < 0 || m >= N) m = m < 0 ? -m : 2 * (N - 1) - m;
+    return m;
 }
 
 // ---- progress counters between warps (same GPU: .gpu scope; another GPU over NVLink: .sys scope) ------------------

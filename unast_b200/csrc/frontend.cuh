@@ -61,6 +61,26 @@ __device__ __forceinline__ float preemph(float cur, float prev) { return __fsub_
 // v[j] = (y[2n] w[2n], y[2n+1] w[2n+1]),  n = lane + 32 j.
 // wbase: index of the utterance's first (trimmed) sample in `wave`; N: trimmed length; t: frame index.
 // For PCM16 the samples are kept as integer-valued floats: the 2^-15 lives in the window table (exact).
+// Edge taps of a clip that one reflection does not cover (<= 1024 samples; numpy.pad reflects repeatedly): out of line, so
+// that the hot kernel carries a call it never takes for LJSpeech-length audio.
+template <bool I16>
+__device__ __noinline__ void edge_taps_general(float* scratch, const void* wave, long long wbase, int N, int n0, int lane) {
+    for (int i = lane; i < WIN; i += 32) {
+        const int m = reflect_index(n0 + i, N);
+        float cur, prev = 0.0f;
+        if constexpr (I16) {
+            const short* s = reinterpret_cast<const short*>(wave) + wbase;
+            cur = (float)s[m];
+            if (m > 0) prev = (float)s[m - 1];
+        } else {
+            const float* s = reinterpret_cast<const float*>(wave) + wbase;
+            cur = s[m];
+            if (m > 0) prev = s[m - 1];
+        }
+        scratch[i] = m > 0 ? preemph(cur, prev) : cur;
+    }
+}
+
 template <class T, bool I16>
 __device__ __forceinline__ void load_frame(cplx_t<T> (&v)[32], const void* __restrict__ wave, long long wbase, int N, int t,
                                            const cplx_t<T>* __restrict__ s_win, float* scratch, int lane) {
@@ -114,8 +134,7 @@ __device__ __forceinline__ void load_frame(cplx_t<T> (&v)[32], const void* __res
         }
     } else {
         // edge frame: reflect padding of librosa.stft(center=True); y[0] = x[0] (np.append(y[0], ...), utils.py:251)
-        auto sample = [&](int m) -> float {                    // pre-emphasised signal at (reflected) index m
-            m = reflect_index(m, N);                              // (clips of <= 1024 samples are reflected more than once)
+        auto sample_at = [&](int m) -> float {                 // pre-emphasised signal at index m in [0, N)
             float cur, prev = 0.0f;
             if constexpr (I16) {
                 const short* s = reinterpret_cast<const short*>(wave) + wbase;
@@ -129,9 +148,19 @@ __device__ __forceinline__ void load_frame(cplx_t<T> (&v)[32], const void* __res
             return m > 0 ? preemph(cur, prev) : cur;
         };
         // compact runtime loop (edge frames are rare; unrolling this path 36x bloats the instruction cache): stage the
-        // taps in the warp's idle exchange buffer, then pick them up with static register indices
+        // taps in the warp's idle exchange buffer, then pick them up with static register indices.  The loop is bound by
+        // the latency of its global loads, so its body stays branch-free (one reflection, what every clip of more than
+        // 1024 samples needs) and unrollable; taps that one reflection does not bring home are redone below.
+        bool again = false;
 #pragma unroll 4
-        for (int i = lane; i < WIN; i += 32) scratch[i] = sample(n0 + i);
+        for (int i = lane; i < WIN; i += 32) {
+            int m = n0 + i;
+            m = m < 0 ? -m : (m >= N ? 2 * (N - 1) - m : m);
+            const bool ok = m >= 0 && m < N;
+            again |= !ok;
+            scratch[i] = sample_at(ok ? m : 0);
+        }
+        if (__any_sync(0xffffffffu, again)) edge_taps_general<I16>(scratch, wave, wbase, N, n0, lane);   // clips of <= 1024 samples
         __syncwarp();
         static_for<0, 18>([&](auto jj) {
             constexpr int j = decltype(jj)::value;

@@ -130,6 +130,27 @@ def test_zero_phase_start_amplifies_last_bit_differences_of_S():
         assert d30 < 110.0
 
 
+def test_short_clips_are_reflected_repeatedly():
+    """numpy.pad(mode="reflect") under librosa.stft / effects.trim reflects a clip of <= 1024 samples more than once; the index
+    rule the CUDA loader restates (period 2 (N - 1), N == 1: constant), checked against numpy itself, and the oracle runs on
+    such clips (1 + N // 275 frames)."""
+    def refl(m, N):
+        if N == 1:
+            return 0
+        P = 2 * (N - 1)
+        m %= P
+        return m if m < N else P - m
+    for N in (1, 2, 3, 275, 600, 1024, 1025):
+        y = np.arange(N, dtype=np.float32) + 1
+        ref = np.pad(y, 1024, mode="reflect")
+        mine = np.array([y[refl(k - 1024, N)] for k in range(N + 2048)], np.float32)
+        assert np.array_equal(ref, mine), N
+    for N in (2, 300, 1024):
+        w = (0.1 * np.random.RandomState(N).randn(N)).astype(np.float32)
+        mel, mag, b = so.spectrograms_from_wave(w, return_bounds=True)
+        assert mel.shape == (1 + (b[1] - b[0]) // 275, 80) and mag.shape[1] == 1025 and 0 <= b[0] < b[1] <= N
+
+
 def test_deemphasis_inverts_preemphasis():
     rng = np.random.RandomState(1)
     y = rng.randn(5000)
